@@ -1,0 +1,121 @@
+#!/usr/bin/env python
+"""Builds the native layer for sm_100a with nvcc (cross-compiles without a GPU).
+
+    python build.py            -> distributed_dot_product/_lib/libddp_b200.so
+    python build.py harness    -> also build/gemm_harness (standalone CUDA validation binary)
+    python build.py sass       -> also profiles/sass/*.sass.txt (SASS mnemonic evidence)
+
+Objects are cached by mtime under build/obj.
+"""
+import concurrent.futures as cf
+import os
+import subprocess
+import sys
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
+FLAGS = ARCH + ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr",
+                "-Xptxas", "-v"]
+LIB_SOURCES = [
+    "csrc/runtime/runtime.cu",
+    "csrc/gemm/gemm_api.cu",
+    "csrc/softmax/softmax.cu",
+]
+HEADERS = [
+    "include/ddp_b200.h",
+    "csrc/common/ptx.cuh",
+    "csrc/common/host_util.h",
+    "csrc/gemm/gemm_sm100.cuh",
+]
+LIB_OUT = "distributed_dot_product/_lib/libddp_b200.so"
+
+
+def _newer(src_list, out):
+    if not os.path.exists(out):
+        return True
+    t = os.path.getmtime(out)
+    return any(os.path.getmtime(os.path.join(ROOT, s)) > t for s in src_list if os.path.exists(os.path.join(ROOT, s)))
+
+
+def _run(cmd, log=None):
+    r = subprocess.run(cmd, cwd=ROOT, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    if log:
+        with open(log, "w") as f:
+            f.write(" ".join(cmd) + "\n" + r.stdout)
+    if r.returncode != 0:
+        sys.stderr.write(r.stdout)
+        raise RuntimeError("command failed: " + " ".join(cmd))
+    return r.stdout
+
+
+def compile_obj(src):
+    obj = os.path.join(ROOT, "build/obj", src.replace("/", "_") + ".o")
+    os.makedirs(os.path.dirname(obj), exist_ok=True)
+    if _newer([src] + HEADERS, obj):
+        _run([NVCC] + FLAGS + ["-c", src, "-o", obj], log=obj + ".log")
+    return obj
+
+
+def build_lib(verbose=True):
+    srcs = [s for s in LIB_SOURCES if os.path.exists(os.path.join(ROOT, s))]
+    with cf.ThreadPoolExecutor(max_workers=4) as ex:
+        objs = list(ex.map(compile_obj, srcs))
+    out = os.path.join(ROOT, LIB_OUT)
+    os.makedirs(os.path.dirname(out), exist_ok=True)
+    if _newer([os.path.relpath(o, ROOT) for o in objs], out):
+        _run([NVCC] + ARCH + ["-shared", "-o", out] + objs + ["-lcudart_static", "-ldl", "-lrt", "-lpthread"])
+    if verbose:
+        print("built", LIB_OUT)
+    return out
+
+
+def build_harness():
+    srcs = [s for s in LIB_SOURCES if os.path.exists(os.path.join(ROOT, s))]
+    objs = [compile_obj(s) for s in srcs]
+    os.makedirs(os.path.join(ROOT, "build"), exist_ok=True)
+    for name in ("gemm_harness",):
+        src = "csrc/tests/%s.cu" % name
+        if not os.path.exists(os.path.join(ROOT, src)):
+            continue
+        out = os.path.join(ROOT, "build", name)
+        if _newer([src] + HEADERS + [os.path.relpath(o, ROOT) for o in objs], out):
+            _run([NVCC] + ARCH + ["-O2", "-std=c++17", src, "-o", out] + objs)
+        print("built build/" + name)
+
+
+def dump_sass():
+    out_dir = os.path.join(ROOT, "profiles/sass")
+    os.makedirs(out_dir, exist_ok=True)
+    lib = os.path.join(ROOT, LIB_OUT)
+    sass = _run(["/usr/local/cuda/bin/cuobjdump", "-sass", lib])
+    import collections
+    import re
+    per_kernel = collections.OrderedDict()
+    cur = None
+    for line in sass.splitlines():
+        m = re.search(r"Function : (\S+)", line)
+        if m:
+            cur = m.group(1)
+            per_kernel[cur] = collections.Counter()
+            continue
+        if cur:
+            m = re.search(r"^\s+/\*[0-9a-f]+\*/\s+(?:@!?U?P\d+\s+)?([A-Z][A-Z0-9_.]+)", line)
+            if m:
+                per_kernel[cur][m.group(1).split(".")[0]] += 1
+    keys = ["UTCHMMA", "UTCQMMA", "UTCMMA", "LDTM", "STTM", "UTMALDG", "UTMASTG", "UBLKCP", "SYNCS", "HMMA", "LDG",
+            "STG", "ATOMG", "RED", "MUFU"]
+    with open(os.path.join(out_dir, "mnemonics.txt"), "w") as f:
+        f.write("# SASS mnemonic counts per kernel in %s (cuobjdump -sass)\n" % LIB_OUT)
+        for k, cnt in per_kernel.items():
+            tc = {m: n for m, n in cnt.items() if any(m.startswith(p) for p in keys)}
+            f.write("%s\n    %s\n" % (k, " ".join("%s=%d" % kv for kv in sorted(tc.items()))))
+    print("wrote profiles/sass/mnemonics.txt (%d kernels)" % len(per_kernel))
+
+
+if __name__ == "__main__":
+    build_lib()
+    if "harness" in sys.argv[1:]:
+        build_harness()
+    if "sass" in sys.argv[1:]:
+        dump_sass()

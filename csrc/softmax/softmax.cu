@@ -1,0 +1,444 @@
+// Row-local kernels of the attention layer (reference: distributed_dot_product/module.py:65-67 and its
+// autograd): fused scale + boolean mask + softmax over the T/N x T score slab, its backward, and the
+// column sum used for bias gradients.  The whole row is local to a rank, so no communication is needed.
+//
+// Two code paths per kernel:
+//   * register-resident: the row lives in registers as packed 16-byte vectors -> one HBM read + one write
+//   * streaming: arbitrary length / alignment, online max+sum then a second (L2-assisted) read.
+// Work item = (outer batch, row); the head loop is innermost so a mask row is re-read from L1/L2, not HBM.
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+
+#include <cfloat>
+#include <cstdint>
+
+#include "../../include/ddp_b200.h"
+#include "../common/host_util.h"
+
+namespace ddp {
+
+struct SmParams {
+  const void* x;  // fwd: scores; bwd: y (probabilities)
+  const void* dy; // bwd only
+  void* out;      // fwd: y; bwd: dx
+  const uint8_t* mask;
+  const float* delta;  // bwd: optional precomputed rowsum(dy*y), [b1][b0][rows]
+  long long x_ld, x_sb0, x_sb1;
+  long long dy_ld, dy_sb0, dy_sb1;
+  long long o_ld, o_sb0, o_sb1;
+  long long m_ld, m_sb1;
+  int rows, cols, b0, b1;
+  float scale;
+};
+
+template <typename T> __device__ __forceinline__ float to_f(T v);
+template <> __device__ __forceinline__ float to_f<float>(float v) { return v; }
+template <> __device__ __forceinline__ float to_f<__nv_bfloat16>(__nv_bfloat16 v) { return __bfloat162float(v); }
+template <> __device__ __forceinline__ float to_f<__half>(__half v) { return __half2float(v); }
+template <typename T> __device__ __forceinline__ T from_f(float v);
+template <> __device__ __forceinline__ float from_f<float>(float v) { return v; }
+template <> __device__ __forceinline__ __nv_bfloat16 from_f<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
+template <> __device__ __forceinline__ __half from_f<__half>(float v) { return __float2half_rn(v); }
+
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+// Block-wide reductions through a small shared array; every thread gets the result.
+template <bool kMax>
+__device__ __forceinline__ float block_reduce(float v, float* red) {
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  v = kMax ? warp_max(v) : warp_sum(v);
+  __syncthreads();  // protect `red` from the previous use
+  if (lane == 0) red[w] = v;
+  __syncthreads();
+  float r = (lane < nw) ? red[lane] : (kMax ? -INFINITY : 0.f);
+  r = kMax ? warp_max(r) : warp_sum(r);
+  return r;
+}
+
+constexpr float kLog2e = 1.4426950408889634f;
+
+// ------------------------------------------------------------------ forward, register resident
+template <typename T, int VPT>
+__global__ void __launch_bounds__(512) softmax_fwd_reg(const SmParams p) {
+  constexpr int VE = 16 / sizeof(T);
+  __shared__ float red[32];
+  const int nvec = p.cols / VE;
+  const int items = p.b1 * p.rows;
+  const float s2 = p.scale * kLog2e;
+  for (int item = blockIdx.x; item < items; item += gridDim.x) {
+    const int b1i = item / p.rows, row = item - b1i * p.rows;
+    const uint8_t* mrow = p.mask ? p.mask + b1i * p.m_sb1 + static_cast<long long>(row) * p.m_ld : nullptr;
+    for (int h = 0; h < p.b0; ++h) {
+      const T* xr = reinterpret_cast<const T*>(p.x) + b1i * p.x_sb1 + h * p.x_sb0 + static_cast<long long>(row) * p.x_ld;
+      T* yr = reinterpret_cast<T*>(p.out) + b1i * p.o_sb1 + h * p.o_sb0 + static_cast<long long>(row) * p.o_ld;
+      uint4 q[VPT];
+#pragma unroll
+      for (int i = 0; i < VPT; ++i) {
+        const int v = threadIdx.x + i * blockDim.x;
+        if (v < nvec) q[i] = *reinterpret_cast<const uint4*>(xr + static_cast<long long>(v) * VE);
+      }
+      float mx = -INFINITY;
+#pragma unroll
+      for (int i = 0; i < VPT; ++i) {
+        const int v = threadIdx.x + i * blockDim.x;
+        if (v < nvec) {
+          T* e = reinterpret_cast<T*>(&q[i]);
+          if (mrow) {
+            uint8_t mb[VE];
+            if constexpr (VE == 8) {
+              *reinterpret_cast<uint2*>(mb) = *reinterpret_cast<const uint2*>(mrow + static_cast<long long>(v) * VE);
+            } else {
+              *reinterpret_cast<uint32_t*>(mb) = *reinterpret_cast<const uint32_t*>(mrow + static_cast<long long>(v) * VE);
+            }
+#pragma unroll
+            for (int k = 0; k < VE; ++k)
+              if (mb[k]) e[k] = from_f<T>(-INFINITY);
+          }
+#pragma unroll
+          for (int k = 0; k < VE; ++k) mx = fmaxf(mx, to_f(e[k]) * p.scale);
+        }
+      }
+      mx = block_reduce<true>(mx, red);
+      const float m2 = mx * kLog2e;
+      float sum = 0.f;
+#pragma unroll
+      for (int i = 0; i < VPT; ++i) {
+        const int v = threadIdx.x + i * blockDim.x;
+        if (v < nvec) {
+          T* e = reinterpret_cast<T*>(&q[i]);
+#pragma unroll
+          for (int k = 0; k < VE; ++k) {
+            const float ex = exp2f(to_f(e[k]) * s2 - m2);  // fully masked row: -inf - -inf = NaN, as the reference
+            sum += ex;
+            e[k] = from_f<T>(ex);
+          }
+        }
+      }
+      sum = block_reduce<false>(sum, red);
+      const float inv = 1.f / sum;
+#pragma unroll
+      for (int i = 0; i < VPT; ++i) {
+        const int v = threadIdx.x + i * blockDim.x;
+        if (v < nvec) {
+          T* e = reinterpret_cast<T*>(&q[i]);
+#pragma unroll
+          for (int k = 0; k < VE; ++k) e[k] = from_f<T>(to_f(e[k]) * inv);
+          *reinterpret_cast<uint4*>(yr + static_cast<long long>(v) * VE) = q[i];
+        }
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------ forward, streaming (any shape)
+template <typename T>
+__global__ void __launch_bounds__(512) softmax_fwd_stream(const SmParams p) {
+  __shared__ float red[32];
+  const int items = p.b1 * p.rows;
+  const float s2 = p.scale * kLog2e;
+  for (int item = blockIdx.x; item < items; item += gridDim.x) {
+    const int b1i = item / p.rows, row = item - b1i * p.rows;
+    const uint8_t* mrow = p.mask ? p.mask + b1i * p.m_sb1 + static_cast<long long>(row) * p.m_ld : nullptr;
+    for (int h = 0; h < p.b0; ++h) {
+      const T* xr = reinterpret_cast<const T*>(p.x) + b1i * p.x_sb1 + h * p.x_sb0 + static_cast<long long>(row) * p.x_ld;
+      T* yr = reinterpret_cast<T*>(p.out) + b1i * p.o_sb1 + h * p.o_sb0 + static_cast<long long>(row) * p.o_ld;
+      float mx = -INFINITY;
+      for (int c = threadIdx.x; c < p.cols; c += blockDim.x) {
+        const float v = (mrow && mrow[c]) ? -INFINITY : to_f(xr[c]) * p.scale;
+        mx = fmaxf(mx, v);
+      }
+      mx = block_reduce<true>(mx, red);
+      const float m2 = mx * kLog2e;
+      float sum = 0.f;
+      for (int c = threadIdx.x; c < p.cols; c += blockDim.x) {
+        const float v = (mrow && mrow[c]) ? -INFINITY : to_f(xr[c]) * s2;
+        sum += exp2f(v - m2);
+      }
+      sum = block_reduce<false>(sum, red);
+      const float inv = 1.f / sum;
+      for (int c = threadIdx.x; c < p.cols; c += blockDim.x) {
+        const float v = (mrow && mrow[c]) ? -INFINITY : to_f(xr[c]) * s2;
+        yr[c] = from_f<T>(exp2f(v - m2) * inv);
+      }
+      __syncthreads();  // in-place safety across heads is per row, nothing shared; keeps `red` reuse simple
+    }
+  }
+}
+
+// ------------------------------------------------------------------ backward, register resident
+template <typename T, int VPT>
+__global__ void __launch_bounds__(512) softmax_bwd_reg(const SmParams p) {
+  constexpr int VE = 16 / sizeof(T);
+  __shared__ float red[32];
+  const int nvec = p.cols / VE;
+  const long long items = static_cast<long long>(p.b1) * p.b0 * p.rows;
+  for (long long item = blockIdx.x; item < items; item += gridDim.x) {
+    const int row = static_cast<int>(item % p.rows);
+    const int bh = static_cast<int>(item / p.rows);
+    const int b1i = bh / p.b0, h = bh - b1i * p.b0;
+    const T* yr = reinterpret_cast<const T*>(p.x) + b1i * p.x_sb1 + h * p.x_sb0 + static_cast<long long>(row) * p.x_ld;
+    const T* gr = reinterpret_cast<const T*>(p.dy) + b1i * p.dy_sb1 + h * p.dy_sb0 + static_cast<long long>(row) * p.dy_ld;
+    T* dr = reinterpret_cast<T*>(p.out) + b1i * p.o_sb1 + h * p.o_sb0 + static_cast<long long>(row) * p.o_ld;
+    uint4 qy[VPT], qg[VPT];
+#pragma unroll
+    for (int i = 0; i < VPT; ++i) {
+      const int v = threadIdx.x + i * blockDim.x;
+      if (v < nvec) {
+        qy[i] = *reinterpret_cast<const uint4*>(yr + static_cast<long long>(v) * VE);
+        qg[i] = *reinterpret_cast<const uint4*>(gr + static_cast<long long>(v) * VE);
+      }
+    }
+    float dot;
+    if (p.delta) {
+      dot = p.delta[item];
+    } else {
+      dot = 0.f;
+#pragma unroll
+      for (int i = 0; i < VPT; ++i) {
+        const int v = threadIdx.x + i * blockDim.x;
+        if (v < nvec) {
+          const T* a = reinterpret_cast<const T*>(&qy[i]);
+          const T* b = reinterpret_cast<const T*>(&qg[i]);
+#pragma unroll
+          for (int k = 0; k < VE; ++k) dot += to_f(a[k]) * to_f(b[k]);
+        }
+      }
+      dot = block_reduce<false>(dot, red);
+    }
+#pragma unroll
+    for (int i = 0; i < VPT; ++i) {
+      const int v = threadIdx.x + i * blockDim.x;
+      if (v < nvec) {
+        const T* a = reinterpret_cast<const T*>(&qy[i]);
+        T* b = reinterpret_cast<T*>(&qg[i]);
+#pragma unroll
+        for (int k = 0; k < VE; ++k) b[k] = from_f<T>(p.scale * to_f(a[k]) * (to_f(b[k]) - dot));
+        *reinterpret_cast<uint4*>(dr + static_cast<long long>(v) * VE) = qg[i];
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------ backward, streaming
+template <typename T, bool kVec>
+__global__ void __launch_bounds__(512) softmax_bwd_stream(const SmParams p) {
+  constexpr int VE = kVec ? 16 / sizeof(T) : 1;
+  __shared__ float red[32];
+  const int nvec = p.cols / VE;
+  const long long items = static_cast<long long>(p.b1) * p.b0 * p.rows;
+  for (long long item = blockIdx.x; item < items; item += gridDim.x) {
+    const int row = static_cast<int>(item % p.rows);
+    const int bh = static_cast<int>(item / p.rows);
+    const int b1i = bh / p.b0, h = bh - b1i * p.b0;
+    const T* yr = reinterpret_cast<const T*>(p.x) + b1i * p.x_sb1 + h * p.x_sb0 + static_cast<long long>(row) * p.x_ld;
+    const T* gr = reinterpret_cast<const T*>(p.dy) + b1i * p.dy_sb1 + h * p.dy_sb0 + static_cast<long long>(row) * p.dy_ld;
+    T* dr = reinterpret_cast<T*>(p.out) + b1i * p.o_sb1 + h * p.o_sb0 + static_cast<long long>(row) * p.o_ld;
+    float dot;
+    if (p.delta) {
+      dot = p.delta[item];
+    } else {
+      dot = 0.f;
+      for (int v = threadIdx.x; v < nvec; v += blockDim.x) {
+        if constexpr (kVec) {
+          const uint4 a4 = *reinterpret_cast<const uint4*>(yr + static_cast<long long>(v) * VE);
+          const uint4 b4 = *reinterpret_cast<const uint4*>(gr + static_cast<long long>(v) * VE);
+          const T* a = reinterpret_cast<const T*>(&a4);
+          const T* b = reinterpret_cast<const T*>(&b4);
+#pragma unroll
+          for (int k = 0; k < VE; ++k) dot += to_f(a[k]) * to_f(b[k]);
+        } else {
+          dot += to_f(yr[v]) * to_f(gr[v]);
+        }
+      }
+      dot = block_reduce<false>(dot, red);
+    }
+    for (int v = threadIdx.x; v < nvec; v += blockDim.x) {
+      if constexpr (kVec) {
+        const uint4 a4 = *reinterpret_cast<const uint4*>(yr + static_cast<long long>(v) * VE);
+        uint4 b4 = *reinterpret_cast<const uint4*>(gr + static_cast<long long>(v) * VE);
+        const T* a = reinterpret_cast<const T*>(&a4);
+        T* b = reinterpret_cast<T*>(&b4);
+#pragma unroll
+        for (int k = 0; k < VE; ++k) b[k] = from_f<T>(p.scale * to_f(a[k]) * (to_f(b[k]) - dot));
+        *reinterpret_cast<uint4*>(dr + static_cast<long long>(v) * VE) = b4;
+      } else {
+        dr[v] = from_f<T>(p.scale * to_f(yr[v]) * (to_f(gr[v]) - dot));
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------ rowdot: delta[r] = sum_c a[r][c]*b[r][c]
+template <typename T>
+__global__ void rowdot_kernel(const T* a, const T* b, float* out, long long rows, int cols, long long a_ld, long long b_ld) {
+  const long long r = static_cast<long long>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (r >= rows) return;
+  const int lane = threadIdx.x & 31;
+  float s = 0.f;
+  for (int c = lane; c < cols; c += 32) s += to_f(a[r * a_ld + c]) * to_f(b[r * b_ld + c]);
+  s = warp_sum(s);
+  if (lane == 0) out[r] = s;
+}
+
+// ------------------------------------------------------------------ column sum (bias gradient)
+template <typename T>
+__global__ void colsum_kernel(const T* x, T* out, long long rows, int cols, long long ld) {
+  __shared__ float part[8][33];
+  const int c = blockIdx.x * 32 + threadIdx.x;
+  float s = 0.f;
+  if (c < cols)
+    for (long long r = threadIdx.y; r < rows; r += 8) s += to_f(x[r * ld + c]);
+  part[threadIdx.y][threadIdx.x] = s;
+  __syncthreads();
+  if (threadIdx.y == 0 && c < cols) {
+    float t = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) t += part[i][threadIdx.x];
+    out[c] = from_f<T>(t);
+  }
+}
+
+static bool aligned16(const void* p, long long ld, long long sb0, long long sb1, int es) {
+  return (reinterpret_cast<uintptr_t>(p) & 15) == 0 && (ld * es) % 16 == 0 && (sb0 * es) % 16 == 0 && (sb1 * es) % 16 == 0;
+}
+
+template <typename T>
+static int launch_fwd(const SmParams& p, bool vec_ok, cudaStream_t st) {
+  constexpr int VE = 16 / sizeof(T);
+  const int items = p.b1 * p.rows;
+  const int sms = ddp_num_sms();
+  const int nvec = p.cols / VE;
+  if (vec_ok && nvec <= 512 * 16) {
+    if (nvec <= 256) {
+      softmax_fwd_reg<T, 2><<<min(items, sms * 8), 128, 0, st>>>(p);
+    } else if (nvec <= 1024) {
+      softmax_fwd_reg<T, 4><<<min(items, sms * 4), 256, 0, st>>>(p);
+    } else if (nvec <= 4096) {
+      softmax_fwd_reg<T, 8><<<min(items, sms * 2), 512, 0, st>>>(p);
+    } else {
+      softmax_fwd_reg<T, 16><<<min(items, sms * 2), 512, 0, st>>>(p);
+    }
+  } else {
+    softmax_fwd_stream<T><<<min(items, sms * 4), p.cols >= 4096 ? 512 : 256, 0, st>>>(p);
+  }
+  return cuda_check(cudaGetLastError(), "softmax_fwd launch");
+}
+
+template <typename T>
+static int launch_bwd(const SmParams& p, bool vec_ok, cudaStream_t st) {
+  constexpr int VE = 16 / sizeof(T);
+  const long long items = static_cast<long long>(p.b1) * p.b0 * p.rows;
+  const int sms = ddp_num_sms();
+  const int nvec = p.cols / VE;
+  const int cap = static_cast<int>(items < (1 << 30) ? items : (1 << 30));
+  if (vec_ok && nvec <= 512 * 8) {
+    if (nvec <= 256) {
+      softmax_bwd_reg<T, 2><<<min(cap, sms * 8), 128, 0, st>>>(p);
+    } else if (nvec <= 1024) {
+      softmax_bwd_reg<T, 4><<<min(cap, sms * 4), 256, 0, st>>>(p);
+    } else {
+      softmax_bwd_reg<T, 8><<<min(cap, sms * 2), 512, 0, st>>>(p);
+    }
+  } else if (vec_ok) {
+    softmax_bwd_stream<T, true><<<min(cap, sms * 2), 512, 0, st>>>(p);
+  } else {
+    softmax_bwd_stream<T, false><<<min(cap, sms * 4), 256, 0, st>>>(p);
+  }
+  return cuda_check(cudaGetLastError(), "softmax_bwd launch");
+}
+
+}  // namespace ddp
+
+using namespace ddp;
+
+static int es_of(int dt) { return dt == DDP_F32 ? 4 : 2; }
+
+extern "C" int ddp_softmax_fwd(const ddp_tensor* x, const ddp_tensor* y, const uint8_t* mask, int64_t mask_ld,
+                               int64_t mask_sb1, float scale, void* stream) {
+  if (x->dtype != y->dtype) return set_error(-4, "softmax: dtype mismatch");
+  if (x->rows != y->rows || x->cols != y->cols || x->b0 != y->b0 || x->b1 != y->b1)
+    return set_error(-4, "softmax: shape mismatch");
+  if (x->rows * x->b1 > INT32_MAX) return set_error(-4, "softmax: too many rows");
+  SmParams p = {};
+  p.x = x->ptr; p.out = y->ptr; p.mask = mask;
+  p.x_ld = x->ld; p.x_sb0 = x->sb0; p.x_sb1 = x->sb1;
+  p.o_ld = y->ld; p.o_sb0 = y->sb0; p.o_sb1 = y->sb1;
+  p.m_ld = mask_ld; p.m_sb1 = mask_sb1;
+  p.rows = (int)x->rows; p.cols = (int)x->cols; p.b0 = (int)x->b0; p.b1 = (int)x->b1;
+  p.scale = scale;
+  const int es = es_of(x->dtype);
+  const int ve = 16 / es;
+  bool vec_ok = aligned16(x->ptr, x->ld, x->sb0, x->sb1, es) && aligned16(y->ptr, y->ld, y->sb0, y->sb1, es) &&
+                (x->cols % ve == 0);
+  if (mask) vec_ok = vec_ok && ((reinterpret_cast<uintptr_t>(mask) % ve) == 0) && (mask_ld % ve == 0) && (mask_sb1 % ve == 0);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  switch (x->dtype) {
+    case DDP_F32: return launch_fwd<float>(p, vec_ok, st);
+    case DDP_BF16: return launch_fwd<__nv_bfloat16>(p, vec_ok, st);
+    default: return launch_fwd<__half>(p, vec_ok, st);
+  }
+}
+
+extern "C" int ddp_softmax_bwd(const ddp_tensor* y, const ddp_tensor* dy, const ddp_tensor* dx, const float* delta,
+                               float scale, void* stream) {
+  if (y->dtype != dy->dtype || y->dtype != dx->dtype) return set_error(-4, "softmax_bwd: dtype mismatch");
+  if (y->rows != dy->rows || y->cols != dy->cols || y->b0 != dy->b0 || y->b1 != dy->b1 || y->rows != dx->rows ||
+      y->cols != dx->cols || y->b0 != dx->b0 || y->b1 != dx->b1)
+    return set_error(-4, "softmax_bwd: shape mismatch");
+  SmParams p = {};
+  p.x = y->ptr; p.dy = dy->ptr; p.out = dx->ptr; p.delta = delta;
+  p.x_ld = y->ld; p.x_sb0 = y->sb0; p.x_sb1 = y->sb1;
+  p.dy_ld = dy->ld; p.dy_sb0 = dy->sb0; p.dy_sb1 = dy->sb1;
+  p.o_ld = dx->ld; p.o_sb0 = dx->sb0; p.o_sb1 = dx->sb1;
+  p.rows = (int)y->rows; p.cols = (int)y->cols; p.b0 = (int)y->b0; p.b1 = (int)y->b1;
+  p.scale = scale;
+  const int es = es_of(y->dtype);
+  const bool vec_ok = aligned16(y->ptr, y->ld, y->sb0, y->sb1, es) && aligned16(dy->ptr, dy->ld, dy->sb0, dy->sb1, es) &&
+                      aligned16(dx->ptr, dx->ld, dx->sb0, dx->sb1, es) && (y->cols % (16 / es) == 0);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  switch (y->dtype) {
+    case DDP_F32: return launch_bwd<float>(p, vec_ok, st);
+    case DDP_BF16: return launch_bwd<__nv_bfloat16>(p, vec_ok, st);
+    default: return launch_bwd<__half>(p, vec_ok, st);
+  }
+}
+
+extern "C" int ddp_rowdot(const ddp_tensor* a, const ddp_tensor* b, float* out, void* stream) {
+  if (a->dtype != b->dtype || a->rows != b->rows || a->cols != b->cols) return set_error(-4, "rowdot: mismatch");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const long long rows = a->rows;
+  const int wpb = 8;
+  const unsigned grid = (unsigned)((rows + wpb - 1) / wpb);
+  switch (a->dtype) {
+    case DDP_F32:
+      rowdot_kernel<float><<<grid, wpb * 32, 0, st>>>((const float*)a->ptr, (const float*)b->ptr, out, rows, (int)a->cols, a->ld, b->ld);
+      break;
+    case DDP_BF16:
+      rowdot_kernel<__nv_bfloat16><<<grid, wpb * 32, 0, st>>>((const __nv_bfloat16*)a->ptr, (const __nv_bfloat16*)b->ptr, out, rows, (int)a->cols, a->ld, b->ld);
+      break;
+    default:
+      rowdot_kernel<__half><<<grid, wpb * 32, 0, st>>>((const __half*)a->ptr, (const __half*)b->ptr, out, rows, (int)a->cols, a->ld, b->ld);
+  }
+  return cuda_check(cudaGetLastError(), "rowdot launch");
+}
+
+extern "C" int ddp_colsum(const ddp_tensor* x, void* out, void* stream) {
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const dim3 block(32, 8);
+  const unsigned grid = (unsigned)((x->cols + 31) / 32);
+  switch (x->dtype) {
+    case DDP_F32: colsum_kernel<float><<<grid, block, 0, st>>>((const float*)x->ptr, (float*)out, x->rows, (int)x->cols, x->ld); break;
+    case DDP_BF16: colsum_kernel<__nv_bfloat16><<<grid, block, 0, st>>>((const __nv_bfloat16*)x->ptr, (__nv_bfloat16*)out, x->rows, (int)x->cols, x->ld); break;
+    default: colsum_kernel<__half><<<grid, block, 0, st>>>((const __half*)x->ptr, (__half*)out, x->rows, (int)x->cols, x->ld);
+  }
+  return cuda_check(cudaGetLastError(), "colsum launch");
+}

@@ -1,0 +1,102 @@
+/* C ABI of libddp_b200.so — the native layer of the B200 distributed-dot-product framework.
+ *
+ * Every entry point takes raw device pointers and a cudaStream_t (passed as void*), returns 0 on
+ * success or a negative error code (ddp_last_error() gives the text), and never synchronises the
+ * host with the device unless stated.  Python binds these through ctypes
+ * (distributed_dot_product/_native.py); C/C++ callers include this header and link the .so.
+ */
+#ifndef DDP_B200_H_
+#define DDP_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DDP_MAX_WORLD 16
+
+/* element types */
+enum { DDP_F16 = 0, DDP_BF16 = 1, DDP_F32 = 2 /* fp32 storage, TF32 tensor-core math */ };
+
+/* distributed products (reference: distributed_dot_product/multiplication/functions.py) */
+enum {
+  DDP_OP_NT = 0, /* C[*,M,T]  = A[*,M,D]  * gather(B)[*,T,D]^T   functions.py:44-99   */
+  DDP_OP_NN = 1, /* C[*,M,D]  = A[*,M,T]  * gather(B)[*,T,D]     functions.py:160-212 */
+  DDP_OP_TN = 2  /* C[*,Tn,D] = sum_p A_p[*,:,rank-block]^T B_p  functions.py:102-148 */
+};
+
+/* A strided view [b1][b0][rows][cols]; strides in ELEMENTS; the column stride is 1. */
+typedef struct ddp_tensor {
+  void* ptr;
+  int64_t rows, cols;
+  int64_t ld;       /* row stride */
+  int64_t b0, b1;   /* batch extents (b0 = inner, e.g. heads; b1 = outer) */
+  int64_t sb0, sb1; /* batch strides */
+  int32_t dtype;    /* DDP_F16 / DDP_BF16 / DDP_F32 */
+  int32_t _pad;
+} ddp_tensor;
+
+/* Peer-memory context of ONE collective call.  world == 1 -> everything else is ignored.
+ * ws[r] / flags[r] / done[r] are device pointers valid on THIS GPU that alias rank r's symmetric
+ * workspace, flag pad and done counters (own rank included). */
+typedef struct ddp_comm {
+  int32_t world, rank;
+  uint32_t seq;        /* call sequence number, identical on all ranks, strictly increasing */
+  int32_t phase_mask;  /* 1 = produce (push / partial GEMM), 2 = consume; 3 = fused (production) */
+  int32_t chunk_rows;  /* staging granularity in rows of the gathered operand (from `offset`) */
+  int32_t _pad;
+  void* ws[DDP_MAX_WORLD];
+  uint32_t* flags[DDP_MAX_WORLD];
+  uint32_t* done[DDP_MAX_WORLD]; /* done[r][q] = last seq rank q finished, stored in rank r's memory */
+  uint32_t* exit_counter;        /* one zero-initialised uint32 in local memory */
+} ddp_comm;
+
+const char* ddp_last_error(void);
+int ddp_version(void);
+int ddp_num_sms(void);
+
+/* Bytes of symmetric workspace / number of uint32 flags one ddp_gemm call needs (0 if world==1). */
+int ddp_gemm_workspace(int op, const ddp_tensor* A, const ddp_tensor* B, int world, int chunk_rows,
+                       size_t* ws_bytes, size_t* n_flags);
+
+/* Fused collective GEMM on tcgen05/TMEM tiles fed by TMA.
+ *   NT: A=[*,M,D]   B=[*,Tn,D]  C=[*,M,world*Tn]   all-gather(B) -> GEMM
+ *   NN: A=[*,M,T]   B=[*,Tn,D]  C=[*,M,D]          all-gather(B) -> GEMM (rank sum in TMEM)
+ *   TN: A=[*,R,T]   B=[*,R,D]   C=[*,Tn,D]         GEMM -> reduce-scatter into the owner's buffer
+ * C = alpha * product (+ bias[col], NT/NN with world==1 only).  bias may be NULL; it has C's dtype.
+ * dbg: 0 in production (bit 0 swaps LBO/SBO of MN-major descriptors; test harness only). */
+int ddp_gemm(int op, const ddp_tensor* A, const ddp_tensor* B, const ddp_tensor* C, float alpha,
+             const void* bias, const ddp_comm* comm, int dbg, void* stream);
+
+/* Row softmax over the last dim of x[b1][b0][rows][cols] with fused scale and boolean mask:
+ *   y = softmax(scale * x  masked_fill(mask, -inf))     (reference: module.py:65-67)
+ * mask is uint8 [b1][rows][cols] (broadcast over b0 = heads), nonzero = masked out; may be NULL.
+ * y may alias x (in place). */
+int ddp_softmax_fwd(const ddp_tensor* x, const ddp_tensor* y, const uint8_t* mask, int64_t mask_ld,
+                    int64_t mask_sb1, float scale, void* stream);
+
+/* dx = scale * y * (dy - delta), delta = rowsum(dy*y) (computed in-kernel when delta == NULL, else read
+ * from the fp32 array delta[b1][b0][rows]);  dx may alias dy.  (autograd of module.py:65-67) */
+int ddp_softmax_bwd(const ddp_tensor* y, const ddp_tensor* dy, const ddp_tensor* dx, const float* delta,
+                    float scale, void* stream);
+
+/* out[r] = sum_c a[r][c] * b[r][c] in fp32; a, b are [rows][cols] views (row strides ld). */
+int ddp_rowdot(const ddp_tensor* a, const ddp_tensor* b, float* out, void* stream);
+
+/* out[c] = sum_r x[r][c]  (bias gradient).  x is [rows][cols] with row stride ld; out has x's dtype. */
+int ddp_colsum(const ddp_tensor* x, void* out, void* stream);
+
+/* ---- symmetric heap (runtime) ------------------------------------------------------------ */
+/* Allocates `bytes` of device memory suitable for peer mapping and returns a 64-byte IPC handle. */
+int ddp_heap_alloc(size_t bytes, void** ptr, void* ipc_handle_out64);
+int ddp_heap_open(const void* ipc_handle64, void** ptr);
+int ddp_heap_close(void* ptr);
+int ddp_heap_free(void* ptr);
+int ddp_memset_async(void* ptr, int value, size_t bytes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DDP_B200_H_ */
