@@ -35,7 +35,7 @@ static int elem_size(int dt) { return dt == DDP_F32 ? 4 : 2; }
 
 // dims/strides innermost first; strides in bytes for dims 1..4.
 static int make_map(CUtensorMap* m, int dt, void* ptr, const uint64_t dims[5], const uint64_t strides[4],
-                    const uint32_t box[5]) {
+                    const uint32_t box[5], bool mn_major) {
   EncodeFn enc = get_encode_fn();
   if (!enc) return set_error(-10, "cuTensorMapEncodeTiled is not available from the driver");
   if (reinterpret_cast<uintptr_t>(ptr) & 15) return set_error(-2, "tensor base address is not 16-byte aligned");
@@ -54,7 +54,10 @@ static int make_map(CUtensorMap* m, int dt, void* ptr, const uint64_t dims[5], c
   const CUtensorMapDataType t = dt == DDP_F32    ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32
                                 : dt == DDP_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16
                                                  : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
-  CUresult r = enc(m, t, 5, ptr, gd, gs, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+  // MN-major tf32 operands only exist in the 32-byte-atom flavour of the 128-byte swizzle.
+  const CUtensorMapSwizzle sw =
+      (mn_major && dt == DDP_F32) ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B;
+  CUresult r = enc(m, t, 5, ptr, gd, gs, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     char buf[256];
@@ -205,11 +208,16 @@ extern "C" int ddp_gemm(int op, const ddp_tensor* A, const ddp_tensor* B, const 
     uint64_t dims[5], strides[4];
     uint32_t box[5] = {1, 1, 1, 1, 1};
     if (op == DDP_OP_TN) {
+      if (world > 1 && (s.M * es) % 16)
+        return set_error(-2, "tn: T/N * element size must be a multiple of 16 bytes (pad the segments)");
       dims[0] = A->cols; dims[1] = 1; dims[2] = A->rows; dims[3] = A->b0; dims[4] = A->b1;
       strides[0] = A->ld * es; strides[1] = A->ld * es; strides[2] = A->sb0 * es; strides[3] = A->sb1 * es;
       box[0] = ch; box[2] = bk;
     } else {
-      const bool clipped = (op == DDP_OP_NN) && world > 1 && ((s.K * es) % 16 == 0);
+      // TMA needs a 16-byte aligned innermost start coordinate, so a rank segment must start on one.
+      if (op == DDP_OP_NN && world > 1 && (s.K * es) % 16)
+        return set_error(-2, "all: T/N * element size must be a multiple of 16 bytes (pad the segments)");
+      const bool clipped = (op == DDP_OP_NN) && world > 1;
       if (clipped) {
         dims[0] = s.K; dims[1] = world; strides[0] = s.K * es;
         p.a_seg_c0 = 0; p.a_seg_c1 = 1;
@@ -223,7 +231,7 @@ extern "C" int ddp_gemm(int op, const ddp_tensor* A, const ddp_tensor* B, const 
     }
     if (A->b0 == 1) strides[2] = strides[1];
     if (A->b1 == 1) strides[3] = strides[2];
-    if (int e = make_map(&p.tmA, dt, A->ptr, dims, strides, box)) return e;
+    if (int e = make_map(&p.tmA, dt, A->ptr, dims, strides, box, op == DDP_OP_TN)) return e;
   }
   // ---- B (local) and B (gathered)
   {
@@ -237,7 +245,7 @@ extern "C" int ddp_gemm(int op, const ddp_tensor* A, const ddp_tensor* B, const 
     }
     if (B->b0 == 1) strides[2] = strides[1];
     if (B->b1 == 1) strides[3] = strides[2];
-    if (int e = make_map(&p.tmB, dt, B->ptr, dims, strides, box)) return e;
+    if (int e = make_map(&p.tmB, dt, B->ptr, dims, strides, box, op != DDP_OP_NT)) return e;
     if (world > 1 && op != DDP_OP_TN) {
       const uint64_t row_bytes = (uint64_t)B->cols * es;
       if (row_bytes % 16) return set_error(-2, "gathered operand rows must be a multiple of 16 bytes");
@@ -245,7 +253,7 @@ extern "C" int ddp_gemm(int op, const ddp_tensor* A, const ddp_tensor* B, const 
         return set_error(-2, "gathered operand is not 16-byte aligned");
       uint64_t gd[5] = {(uint64_t)B->cols, 1, (uint64_t)B->rows, Bt, (uint64_t)world};
       uint64_t gs[4] = {row_bytes, row_bytes, row_bytes * B->rows, row_bytes * B->rows * Bt};
-      if (int e = make_map(&p.tmBg, dt, comm->ws[rank], gd, gs, box)) return e;
+      if (int e = make_map(&p.tmBg, dt, comm->ws[rank], gd, gs, box, op != DDP_OP_NT)) return e;
       p.push_src = static_cast<const char*>(B->ptr);
       p.push_ld = B->ld * es; p.push_sb0 = B->sb0 * es; p.push_sb1 = B->sb1 * es;
       p.push_rows = (int)B->rows; p.push_row_bytes = (int)row_bytes;

@@ -310,8 +310,12 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
       int acc = 0;
       uint32_t acc_phase = 0;
       const bool swap = (p.dbg & 1) != 0;
-      const uint32_t mn_lbo = swap ? 1024u : static_cast<uint32_t>(BK * 128);
-      const uint32_t mn_sbo = swap ? static_cast<uint32_t>(BK * 128) : 1024u;
+      // MN-major canonical layouts: 16-bit types use 8-row K groups (1024 B apart) under the 16B-chunk
+      // swizzle; tf32 must use the 32B-chunk swizzle whose K groups are 4 rows (512 B apart).
+      constexpr uint32_t kMnType = (DT == DDP_F32) ? 1u : 2u;
+      const uint32_t kMnGroup = (DT == DDP_F32 && !(p.dbg & 2)) ? 512u : 1024u;
+      const uint32_t mn_lbo = swap ? kMnGroup : static_cast<uint32_t>(BK * 128);
+      const uint32_t mn_sbo = swap ? static_cast<uint32_t>(BK * 128) : kMnGroup;
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
         mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
         tc_fence_after();
@@ -323,9 +327,9 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
           const uint32_t sb = sa + kStageABytes;
 #pragma unroll
           for (int kk = 0; kk < BK / UK; ++kk) {
-            const uint64_t adesc = A_MN ? umma_smem_desc(sa + kk * UK * 128, mn_lbo, mn_sbo)
+            const uint64_t adesc = A_MN ? umma_smem_desc(sa + kk * UK * 128, mn_lbo, mn_sbo, kMnType)
                                         : umma_smem_desc(sa + kk * 32, 16, 1024);
-            const uint64_t bdesc = B_MN ? umma_smem_desc(sb + kk * UK * 128, mn_lbo, mn_sbo)
+            const uint64_t bdesc = B_MN ? umma_smem_desc(sb + kk * UK * 128, mn_lbo, mn_sbo, kMnType)
                                         : umma_smem_desc(sb + kk * 32, 16, 1024);
             umma_ss<DT == DDP_F32>(d_tmem, adesc, bdesc, kIdesc, (it | kk) != 0 ? 1u : 0u);
           }

@@ -303,6 +303,14 @@ int main(int argc, char** argv) {
   CK(cudaGetDeviceProperties(&prop, 0));
   printf("device: %s sm_%d%d, %d SMs\n", prop.name, prop.major, prop.minor, prop.multiProcessorCount);
 
+  if (mode == "one" && argc >= 13) {
+    Case c;
+    c.op = atoi(argv[2]); c.dt = atoi(argv[3]); c.world = atoi(argv[4]); c.b1 = atoi(argv[5]); c.b0 = atoi(argv[6]);
+    c.M = atoi(argv[7]); c.Tn = atoi(argv[8]); c.D = atoi(argv[9]); c.interleave = atoi(argv[10]) != 0;
+    c.pad = atoi(argv[11]); c.chunk = atoi(argv[12]); c.val = 2;
+    run_case(c, argc > 13 ? atoi(argv[13]) : 0, true);
+    return g_fail ? 1 : 0;
+  }
   if (mode != "perf") {
     // ---- stage 1: the smallest K-major case; if this fails nothing else is meaningful
     const int dts[3] = {DDP_BF16, DDP_F32, DDP_F16};
@@ -315,13 +323,13 @@ int main(int argc, char** argv) {
       run_case({DDP_OP_NT, dt, 1, 1, 4, 150, 150, 32, true, 0, 64, 2}, 0, true);
       // NN (B MN-major)
       if (!run_case({DDP_OP_NN, dt, 1, 1, 1, 128, 128, 64, false, 0, 64, 2}, 0, true))
-        run_case({DDP_OP_NN, dt, 1, 1, 1, 128, 128, 64, false, 0, 64, 2}, 1, true);
+        for (int dbg = 1; dbg < 4; ++dbg) run_case({DDP_OP_NN, dt, 1, 1, 1, 128, 128, 64, false, 0, 64, 2}, dbg, true);
       run_case({DDP_OP_NN, dt, 1, 1, 1, 128, 256, 128, false, 0, 64, 2}, 0, true);
       run_case({DDP_OP_NN, dt, 1, 2, 2, 200, 328, 264, false, 8, 64, 2}, 0, true);
       run_case({DDP_OP_NN, dt, 1, 1, 4, 100, 160, 32, true, 0, 64, 2}, 0, true);
       // TN (both MN-major)
       if (!run_case({DDP_OP_TN, dt, 1, 1, 1, 0, 128, 64, false, 0, 64, 2}, 0, true))
-        run_case({DDP_OP_TN, dt, 1, 1, 1, 0, 128, 64, false, 0, 64, 2}, 1, true);
+        for (int dbg = 1; dbg < 4; ++dbg) run_case({DDP_OP_TN, dt, 1, 1, 1, 0, 128, 64, false, 0, 64, 2}, dbg, true);
       run_case({DDP_OP_TN, dt, 1, 1, 1, 0, 256, 128, false, 0, 64, 2}, 0, true);
       run_case({DDP_OP_TN, dt, 1, 2, 2, 0, 200, 264, false, 8, 64, 2}, 0, true);
       run_case({DDP_OP_TN, dt, 1, 1, 4, 0, 136, 32, true, 0, 64, 2}, 0, true);
@@ -336,6 +344,7 @@ int main(int argc, char** argv) {
         run_case({DDP_OP_NN, dt, W, 1, 2, 128, 128, 64, false, 0, 64, 2}, 0, true);
         run_case({DDP_OP_NN, dt, W, 2, 2, 96, 96, 64, true, 0, 32, 2}, 0, true);
         run_case({DDP_OP_NN, dt, W, 1, 1, 328, 328, 96, false, 0, 100, 2}, 0, true);
+        run_case({DDP_OP_NT, dt, W, 1, 2, 100, 100, 72, false, 0, 64, 2}, 0, true);
         run_case({DDP_OP_TN, dt, W, 1, 2, 0, 128, 64, false, 0, 64, 2}, 0, true);
         run_case({DDP_OP_TN, dt, W, 2, 2, 0, 96, 64, true, 0, 32, 2}, 0, true);
         run_case({DDP_OP_TN, dt, W, 1, 1, 0, 328, 96, false, 0, 100, 2}, 0, true);

@@ -1,0 +1,93 @@
+# -*- coding: utf-8 -*-
+"""ctypes binding of libddp_b200.so (C ABI in include/ddp_b200.h).
+
+The library is built in-tree by ``build.py`` (nvcc, sm_100a) and loaded lazily the first time a CUDA
+tensor reaches one of the ops.  On a machine with a GPU a missing library is a hard error: the ops
+never fall back to PyTorch kernels silently.
+"""
+import ctypes
+import os
+import threading
+
+MAX_WORLD = 16
+F16, BF16, F32 = 0, 1, 2
+OP_NT, OP_NN, OP_TN = 0, 1, 2
+
+_LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), '_lib', 'libddp_b200.so')
+_lib = None
+_lock = threading.Lock()
+
+
+class Tensor(ctypes.Structure):
+    _fields_ = [('ptr', ctypes.c_void_p), ('rows', ctypes.c_int64), ('cols', ctypes.c_int64),
+                ('ld', ctypes.c_int64), ('b0', ctypes.c_int64), ('b1', ctypes.c_int64),
+                ('sb0', ctypes.c_int64), ('sb1', ctypes.c_int64), ('dtype', ctypes.c_int32),
+                ('_pad', ctypes.c_int32)]
+
+
+class Comm(ctypes.Structure):
+    _fields_ = [('world', ctypes.c_int32), ('rank', ctypes.c_int32), ('seq', ctypes.c_uint32),
+                ('phase_mask', ctypes.c_int32), ('chunk_rows', ctypes.c_int32), ('_pad', ctypes.c_int32),
+                ('ws', ctypes.c_void_p * MAX_WORLD), ('flags', ctypes.c_void_p * MAX_WORLD),
+                ('done', ctypes.c_void_p * MAX_WORLD), ('exit_counter', ctypes.c_void_p)]
+
+
+class NativeError(RuntimeError):
+    pass
+
+
+def lib_path():
+    return _LIB_PATH
+
+
+def available():
+    return os.path.exists(_LIB_PATH)
+
+
+def load():
+    """Returns the loaded library, building nothing: raises if the .so is absent."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    with _lock:
+        if _lib is not None:
+            return _lib
+        if not os.path.exists(_LIB_PATH):
+            raise NativeError(
+                'libddp_b200.so not found at %s - run `python build.py` (nvcc, sm_100a) first; '
+                'CUDA tensors are never routed to a PyTorch fallback' % _LIB_PATH)
+        lib = ctypes.CDLL(_LIB_PATH)
+        c = ctypes
+        tp = c.POINTER(Tensor)
+        lib.ddp_last_error.restype = c.c_char_p
+        lib.ddp_version.restype = c.c_int
+        lib.ddp_num_sms.restype = c.c_int
+        lib.ddp_gemm_workspace.argtypes = [c.c_int, tp, tp, c.c_int, c.c_int, c.POINTER(c.c_size_t),
+                                           c.POINTER(c.c_size_t)]
+        lib.ddp_gemm.argtypes = [c.c_int, tp, tp, tp, c.c_float, c.c_void_p, c.POINTER(Comm), c.c_int,
+                                 c.c_void_p]
+        lib.ddp_softmax_fwd.argtypes = [tp, tp, c.c_void_p, c.c_int64, c.c_int64, c.c_float, c.c_void_p]
+        lib.ddp_softmax_bwd.argtypes = [tp, tp, tp, c.c_void_p, c.c_float, c.c_void_p]
+        lib.ddp_rowdot.argtypes = [tp, tp, c.c_void_p, c.c_void_p]
+        lib.ddp_colsum.argtypes = [tp, c.c_void_p, c.c_void_p]
+        lib.ddp_heap_alloc.argtypes = [c.c_size_t, c.POINTER(c.c_void_p), c.c_void_p]
+        lib.ddp_heap_open.argtypes = [c.c_void_p, c.POINTER(c.c_void_p)]
+        lib.ddp_heap_close.argtypes = [c.c_void_p]
+        lib.ddp_heap_free.argtypes = [c.c_void_p]
+        lib.ddp_memset_async.argtypes = [c.c_void_p, c.c_int, c.c_size_t, c.c_void_p]
+        _lib = lib
+    return _lib
+
+
+def check(code):
+    if code != 0:
+        raise NativeError('libddp_b200 error %d: %s' % (code, load().ddp_last_error().decode()))
+
+
+#: number of kernels launched through this binding (bench.py reports it as ``gpu_launches``)
+launch_count = 0
+
+
+def count_launch(n=1):
+    global launch_count
+    launch_count += n

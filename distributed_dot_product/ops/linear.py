@@ -1,0 +1,57 @@
+# -*- coding: utf-8 -*-
+"""Projection layers on the framework's own tcgen05 GEMM (reference: module.py:43-45,75 use
+``nn.Linear`` -> cuBLAS).
+
+``y = x W^T + b`` is the NT kernel with the bias fused in the epilogue; ``dx = dy W`` is the NN kernel;
+``dW = dy^T x`` is the TN kernel (both operands MN-major straight from their row-major storage, no
+transpose pass); ``db`` is a column-sum kernel.  Weight gradients stay rank-partial, as in the
+reference (tests/test_gradient.py:116-121).
+"""
+import ctypes
+
+import torch
+import torch.nn.functional as F
+
+from distributed_dot_product import _native
+from distributed_dot_product.ops import gemm as _g
+
+
+def _colsum(x2):
+    lib = _native.load()
+    out = torch.empty(x2.size(-1), dtype=x2.dtype, device=x2.device)
+    v = _g.as_view(x2.unsqueeze(0).unsqueeze(0))
+    _native.check(lib.ddp_colsum(ctypes.byref(v), ctypes.c_void_p(out.data_ptr()), _g._stream()))
+    _native.count_launch()
+    return out
+
+
+class _Linear(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias):
+        ctx.save_for_backward(x, weight)
+        ctx.has_bias = bias is not None
+        x2 = x.reshape(-1, x.size(-1))
+        y = _g.gemm(_native.OP_NT, x2, weight, bias=bias, distributed=False)
+        return y.reshape(tuple(x.shape[:-1]) + (weight.size(0),))
+
+    @staticmethod
+    def backward(ctx, gy):
+        x, weight = ctx.saved_tensors
+        g2 = gy.reshape(-1, gy.size(-1))
+        x2 = x.reshape(-1, x.size(-1))
+        gx = gw = gb = None
+        if ctx.needs_input_grad[0]:
+            gx = _g.gemm(_native.OP_NN, g2, weight, distributed=False).reshape(x.shape)
+        if ctx.needs_input_grad[1]:
+            gw = _g.gemm(_native.OP_TN, g2, x2, distributed=False)
+        if ctx.has_bias and ctx.needs_input_grad[2]:
+            g2c = g2 if g2.stride(-1) == 1 else g2.contiguous()
+            gb = _colsum(g2c)
+        return gx, gw, gb
+
+
+def linear(x, weight, bias=None):
+    """``F.linear`` semantics; CUDA tensors of a tensor-core dtype run on the sm_100a GEMM kernels."""
+    if x.is_cuda and x.dtype in _g._DT and weight.dtype == x.dtype:
+        return _Linear.apply(x, weight, bias)
+    return F.linear(x, weight, bias)

@@ -1,0 +1,212 @@
+# -*- coding: utf-8 -*-
+"""Process bootstrap and the symmetric heap behind the fused collective kernels.
+
+Replaces the reference's import-time ``hvd.init()`` + MPI world
+(reference: distributed_dot_product/utils/comm.py:3-10, module.py:19) with
+
+* a lazy, torchrun-style bootstrap (``RANK`` / ``WORLD_SIZE`` / ``LOCAL_RANK`` / ``MASTER_ADDR``),
+  one process per GPU; ``torch.distributed`` is used only for rendezvous, handle exchange and the
+  CPU/gloo plumbing path;
+* a **symmetric heap**: every rank allocates the same layout with the native allocator, exchanges
+  CUDA IPC handles once, and maps every peer's heap, so kernels address remote workspaces and flag
+  pads directly over NVLink / NVSwitch;
+* a monotonically increasing call sequence number shared by all ranks (SPMD call order), used by the
+  kernels as the flag epoch: flags are never reset, workspaces are double buffered by ``seq & 1``.
+"""
+import ctypes
+import os
+import threading
+
+import torch
+import torch.distributed as dist
+
+from distributed_dot_product import _native
+
+_state = {
+    'initialized': False,
+    'world': 1,
+    'rank': 0,
+    'local_rank': 0,
+    'group': None,
+    'owns_pg': False,
+}
+_lock = threading.RLock()
+
+
+def _env_int(name, default):
+    try:
+        return int(os.environ.get(name, default))
+    except ValueError:
+        return default
+
+
+def init(backend=None, device=None):
+    """Initialises the runtime (idempotent).  Called lazily by every public entry point.
+
+    * ``torch.distributed`` already initialised -> reuse the default group;
+    * ``WORLD_SIZE > 1`` in the environment (torchrun) -> ``init_process_group`` with NCCL when CUDA
+      is available, gloo otherwise, and bind this process to ``cuda:LOCAL_RANK``;
+    * otherwise a single-process world of size 1.
+    """
+    with _lock:
+        if _state['initialized']:
+            return
+        if dist.is_available() and dist.is_initialized():
+            _state['world'] = dist.get_world_size()
+            _state['rank'] = dist.get_rank()
+            _state['local_rank'] = _env_int('LOCAL_RANK', _state['rank'])
+        elif _env_int('WORLD_SIZE', 1) > 1:
+            use_cuda = torch.cuda.is_available()
+            _state['local_rank'] = _env_int('LOCAL_RANK', _env_int('RANK', 0))
+            if use_cuda:
+                torch.cuda.set_device(_state['local_rank'] % torch.cuda.device_count())
+            if backend is None:
+                backend = 'cuda:nccl,cpu:gloo' if use_cuda else 'gloo'
+            os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
+            os.environ.setdefault('MASTER_PORT', '29533')
+            kwargs = {}
+            if use_cuda:
+                kwargs['device_id'] = torch.device('cuda', torch.cuda.current_device())
+            try:
+                dist.init_process_group(backend=backend, **kwargs)
+            except TypeError:
+                dist.init_process_group(backend=backend)
+            _state['owns_pg'] = True
+            _state['world'] = dist.get_world_size()
+            _state['rank'] = dist.get_rank()
+        _state['initialized'] = True
+
+
+def shutdown():
+    """Releases the symmetric heap and, if this module created it, the process group."""
+    with _lock:
+        heap = _Heap._instance
+        if heap is not None:
+            heap.release()
+            _Heap._instance = None
+        if _state['owns_pg'] and dist.is_initialized():
+            dist.destroy_process_group()
+        _state.update(initialized=False, world=1, rank=0, local_rank=0, owns_pg=False)
+
+
+def get_world_size():
+    init()
+    return _state['world']
+
+
+def get_rank():
+    init()
+    return _state['rank']
+
+
+def get_local_rank():
+    init()
+    return _state['local_rank']
+
+
+def barrier():
+    """Host-side barrier (the kernels themselves synchronise with device-side flags)."""
+    init()
+    if _state['world'] > 1:
+        dist.barrier()
+
+
+def _align(x, a):
+    return (x + a - 1) // a * a
+
+
+class _Heap(object):
+    """One symmetric allocation per rank:
+
+        [ done counters : 256 B ][ exit counter : 256 B ]
+        [ parity 0 : workspace | flags ][ parity 1 : workspace | flags ]
+
+    Offsets are identical on every rank because every rank sizes it from the same (SPMD) request.
+    """
+    _instance = None
+    HEADER = 512
+    GRANULE = 64 << 20
+
+    def __init__(self):
+        self.ws_cap = 0
+        self.flag_cap = 0
+        self.base = None          # own allocation (int address)
+        self.peers = []           # addresses of every rank's heap as mapped here (own included)
+        self.seq = 0
+        self.comm = [None, None]  # prebuilt ctypes structs per parity
+        self.generation = 0
+
+    @classmethod
+    def get(cls):
+        if cls._instance is None:
+            cls._instance = _Heap()
+        return cls._instance
+
+    def release(self):
+        if self.base is None:
+            return
+        lib = _native.load()
+        torch.cuda.synchronize()
+        if _state['world'] > 1 and dist.is_initialized():
+            dist.barrier()
+        for r, p in enumerate(self.peers):
+            if r != _state['rank'] and p:
+                lib.ddp_heap_close(ctypes.c_void_p(p))
+        lib.ddp_heap_free(ctypes.c_void_p(self.base))
+        self.base = None
+        self.peers = []
+        self.ws_cap = self.flag_cap = 0
+
+    def ensure(self, ws_bytes, n_flags):
+        """Collective when it has to grow: every rank passes the same sizes in the same call."""
+        if ws_bytes <= self.ws_cap and n_flags <= self.flag_cap:
+            return
+        lib = _native.load()
+        world, rank = _state['world'], _state['rank']
+        new_ws = max(_align(int(ws_bytes * 1.25), self.GRANULE), self.ws_cap)
+        new_flags = max(_align(int(n_flags * 1.25), 1 << 16), self.flag_cap, 1 << 16)
+        self.release()
+        parity_bytes = new_ws + _align(new_flags * 4, 256)
+        total = self.HEADER + 2 * parity_bytes
+        ptr = ctypes.c_void_p()
+        handle = ctypes.create_string_buffer(64)
+        _native.check(lib.ddp_heap_alloc(total, ctypes.byref(ptr), handle))
+        self.base = ptr.value
+        handles = [None] * world
+        dist.all_gather_object(handles, bytes(handle.raw))
+        self.peers = []
+        for r in range(world):
+            if r == rank:
+                self.peers.append(self.base)
+            else:
+                p = ctypes.c_void_p()
+                buf = ctypes.create_string_buffer(handles[r], 64)
+                _native.check(lib.ddp_heap_open(buf, ctypes.byref(p)))
+                self.peers.append(p.value)
+        torch.cuda.synchronize()
+        dist.barrier()
+        self.ws_cap, self.flag_cap = new_ws, new_flags
+        self.seq = 0
+        self.generation += 1
+        for parity in (0, 1):
+            cm = _native.Comm()
+            cm.world, cm.rank, cm.phase_mask = world, rank, 3
+            off = self.HEADER + parity * parity_bytes
+            for r in range(world):
+                cm.ws[r] = self.peers[r] + off
+                cm.flags[r] = self.peers[r] + off + new_ws
+                cm.done[r] = self.peers[r]
+            cm.exit_counter = self.base + 256
+            self.comm[parity] = cm
+
+    def next_comm(self, chunk_rows):
+        self.seq += 1
+        cm = self.comm[self.seq & 1]
+        cm.seq = self.seq
+        cm.chunk_rows = int(chunk_rows)
+        return cm
+
+
+def heap():
+    init()
+    return _Heap.get()

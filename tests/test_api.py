@@ -1,0 +1,119 @@
+# -*- coding: utf-8 -*-
+"""Public surface parity with the reference package."""
+import inspect
+
+import pytest
+import torch
+
+
+def test_import_paths_and_version():
+    import distributed_dot_product as pkg
+    from distributed_dot_product.module import DistributedDotProductAttn  # noqa: F401
+    from distributed_dot_product.multiplication.functions import (  # noqa: F401
+        distributed_matmul_all, distributed_matmul_nt, distributed_matmul_tn, measure, DEBUG)
+    from distributed_dot_product.multiplication.ops import (  # noqa: F401
+        FullMultiplication, LeftTransposeMultiplication, RightTransposeMultiplication)
+    from distributed_dot_product.utils.comm import (  # noqa: F401
+        get_rank, get_world_size, is_main_process, synchronize)
+    assert pkg.VERSION_INFO[:3] == (0, 1, 0)
+    assert pkg.__version__.startswith('0.1.0')
+
+
+def test_signatures_match_reference():
+    from distributed_dot_product.module import DistributedDotProductAttn
+    from distributed_dot_product.multiplication import functions as F
+    sig = inspect.signature(DistributedDotProductAttn.__init__)
+    assert list(sig.parameters)[1:] == ['key_dim', 'value_dim', 'query_dim', 'num_heads', 'add_bias', 'offset',
+                                        'distributed']
+    assert sig.parameters['offset'].default == 32 and sig.parameters['distributed'].default is True
+    fwd = inspect.signature(DistributedDotProductAttn.forward)
+    assert list(fwd.parameters)[1:] == ['keys', 'queries', 'values', 'attn_mask']
+    assert list(inspect.signature(F.distributed_matmul_nt).parameters)[:3] == ['left', 'right', 'offset']
+    assert list(inspect.signature(F.distributed_matmul_all).parameters)[:3] == ['left', 'right', 'offset']
+    assert list(inspect.signature(F.distributed_matmul_tn).parameters)[:2] == ['left', 'right']
+    assert inspect.signature(F.distributed_matmul_nt).parameters['offset'].default == 32
+
+
+@pytest.mark.parametrize('bias', [False, True])
+def test_state_dict_layout(bias):
+    from distributed_dot_product.module import DistributedDotProductAttn
+    m = DistributedDotProductAttn(8, value_dim=16, query_dim=12, add_bias=bias)
+    keys = list(m.state_dict().keys())
+    if bias:
+        assert keys == ['keys.weight', 'keys.bias', 'queries.weight', 'queries.bias', 'values.weight',
+                        'values.bias', 'composition.weight', 'composition.bias']
+    else:
+        assert keys == ['keys.weight', 'queries.weight', 'values.weight', 'composition.weight']
+    sd = m.state_dict()
+    assert tuple(sd['keys.weight'].shape) == (8, 8)
+    assert tuple(sd['queries.weight'].shape) == (8, 12)
+    assert tuple(sd['values.weight'].shape) == (16, 16)
+    assert tuple(sd['composition.weight'].shape) == (16, 16)
+    # a reference-shaped state_dict loads
+    m2 = DistributedDotProductAttn(8, value_dim=16, query_dim=12, add_bias=bias, distributed=False)
+    m2.load_state_dict({k: v.clone() for k, v in sd.items()})
+
+
+def test_constructor_constraints():
+    from distributed_dot_product.module import DistributedDotProductAttn
+    with pytest.raises(AssertionError):
+        DistributedDotProductAttn(10, num_heads=4)
+    with pytest.raises(ValueError):
+        DistributedDotProductAttn(8, value_dim=16, num_heads=2)
+    m = DistributedDotProductAttn(8, num_heads=2, offset=7)
+    assert m.dim == 4 and m.offset == 7 and m.num_heads == 2 and m.value_dim == 8
+
+
+def test_float_mask_raises_and_none_mask_ok():
+    from distributed_dot_product.module import DistributedDotProductAttn
+    m = DistributedDotProductAttn(8)
+    x = torch.rand(1, 5, 8)
+    with pytest.raises(RuntimeError):
+        m(x, x, x, torch.zeros(1, 5, 5))
+    assert m(x, x, x, None).shape == (1, 5, 8)
+
+
+def test_fully_masked_row_is_nan_like_reference():
+    from distributed_dot_product.module import DistributedDotProductAttn
+    m = DistributedDotProductAttn(8)
+    x = torch.rand(1, 4, 8)
+    mask = torch.zeros(1, 4, 4, dtype=torch.bool)
+    mask[0, 2] = True
+    out = m(x, x, x, mask)
+    assert torch.isnan(out[0, 2]).all() and not torch.isnan(out[0, 0]).any()
+
+
+def test_comm_single_process():
+    from distributed_dot_product.utils import comm
+    assert comm.get_world_size() == 1 and comm.get_rank() == 0 and comm.is_main_process()
+    comm.synchronize()
+
+
+def test_single_process_functions_match_dense():
+    from distributed_dot_product.multiplication.functions import (
+        distributed_matmul_all, distributed_matmul_nt, distributed_matmul_tn)
+    a = torch.arange(2 * 5 * 6).view(2, 5, 6)
+    b = torch.arange(2 * 5 * 6).view(2, 5, 6) - 7
+    s = torch.arange(2 * 5 * 5).view(2, 5, 5)
+    assert (distributed_matmul_nt(a, b, offset=2) == a.matmul(b.transpose(-1, -2))).all()
+    assert (distributed_matmul_all(s, b, offset=4) == s.matmul(b)).all()
+    assert (distributed_matmul_tn(s, b) == s.transpose(-1, -2).matmul(b)).all()
+    # input dtype is preserved (the reference returns fp32 for nt/all regardless: SURVEY Q3)
+    for dt in (torch.float64, torch.float32, torch.bfloat16, torch.int64):
+        assert distributed_matmul_nt(a.to(dt), b.to(dt)).dtype == dt
+        assert distributed_matmul_all(s.to(dt), b.to(dt)).dtype == dt
+        assert distributed_matmul_tn(s.to(dt), b.to(dt)).dtype == dt
+
+
+def test_debug_measure_prints(capsys, monkeypatch):
+    from distributed_dot_product.multiplication import functions as F
+    monkeypatch.setattr(F, 'DEBUG', True)
+    a = torch.rand(1, 4, 3)
+    F.distributed_matmul_nt(a, a)
+    out = capsys.readouterr().out
+    assert 'distributed_matmul_nt - Left' in out and 'elapsed time' in out
+
+
+def test_native_library_contract():
+    from distributed_dot_product import _native
+    assert _native.lib_path().endswith('libddp_b200.so')
