@@ -1,0 +1,271 @@
+#!/usr/bin/env python
+# -*- coding: utf-8 -*-
+"""Flagship benchmark: fwd+bwd of DistributedDotProductAttn (BASELINE.json config 4 per-rank shape).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--T total_len]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+Model: 16 heads, d_model = 1024, batch 1, bf16, T/N = 8192 rows per GPU (T = 8192 * N; N = 8 is the named
+T = 65536 config).  Synthetic random inputs, random-init weights.  One step = forward + backward of the whole
+layer (4 projections, K Q^T, scale+mask+softmax, attn V and all their gradients).
+
+Prints ONE JSON line (rank 0).  ``value`` = ms per fwd+bwd step, device-timed with CUDA events around K steps,
+max over ranks.  ``e2e`` = the same through the public API including, every step, the pinned-host -> device copy
+of the step's activations and target and the device -> host read of the loss.
+
+``--impl reference`` runs the unmodified reference from baseline/_ref (Horovod/mpi4py replaced by the
+torch.distributed shim in baseline/shim) on the same shapes in its native dtype (fp32).
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+
+HEADS = 16
+D_MODEL = 1024
+ROWS_PER_GPU = 8192
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=10)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--impl', type=str, default='ours', choices=['ours', 'reference'])
+    ap.add_argument('--T', type=int, default=0, help='total sequence length (default 8192 * gpus)')
+    ap.add_argument('--heads', type=int, default=HEADS)
+    ap.add_argument('--d-model', type=int, default=D_MODEL)
+    ap.add_argument('--offset', type=int, default=1024)
+    ap.add_argument('--dtype', type=str, default='bf16')
+    return ap.parse_args()
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons of this process's GPU during the timed region (NVML)."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index = index
+        self.stop_flag = threading.Event()
+        self.sm, self.reasons, self.max_mhz, self.power = [], set(), None, []
+        self.ok = False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception:
+            self.ok = False
+
+    def run(self):
+        if not self.ok:
+            return
+        nv = self.nv
+        names = {
+            getattr(nv, 'nvmlClocksThrottleReasonHwSlowdown', 0x8): 'hw_slowdown',
+            getattr(nv, 'nvmlClocksThrottleReasonHwThermalSlowdown', 0x40): 'hw_thermal_slowdown',
+            getattr(nv, 'nvmlClocksThrottleReasonSwThermalSlowdown', 0x20): 'sw_thermal_slowdown',
+            getattr(nv, 'nvmlClocksThrottleReasonSwPowerCap', 0x4): 'sw_power_cap',
+            getattr(nv, 'nvmlClocksThrottleReasonHwPowerBrakeSlowdown', 0x80): 'hw_power_brake',
+        }
+        while not self.stop_flag.is_set():
+            try:
+                self.sm.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+                self.power.append(nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0)
+            except Exception:
+                pass
+            time.sleep(0.05)
+
+    def summary(self):
+        if not self.ok or not self.sm:
+            return {'sm_mhz': None, 'sm_max_mhz': self.max_mhz, 'reasons': ['unavailable']}
+        s = sorted(self.sm)
+        return {'sm_mhz': s[len(s) // 2], 'sm_max_mhz': self.max_mhz, 'reasons': sorted(self.reasons),
+                'power_w_max': max(self.power) if self.power else None, 'samples': len(s)}
+
+
+def physical_gpu_index(local_rank):
+    vis = os.environ.get('CUDA_VISIBLE_DEVICES')
+    if vis:
+        try:
+            return int(vis.split(',')[local_rank])
+        except Exception:
+            return local_rank
+    return local_rank
+
+
+def main():
+    args = parse()
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    rank = int(os.environ.get('RANK', '0'))
+    local_rank = int(os.environ.get('LOCAL_RANK', '0'))
+    if args.gpus != world and world == 1 and args.gpus > 1:
+        # convenience: re-exec under torchrun when asked for N > 1 without a launcher
+        os.execvp(sys.executable, [sys.executable, '-m', 'torch.distributed.run', '--nnodes=1',
+                                   '--nproc-per-node', str(args.gpus), '--master-addr', '127.0.0.1',
+                                   '--master-port', '29577', os.path.abspath(__file__)] + sys.argv[1:])
+    reference = args.impl == 'reference'
+    if reference:
+        ref_dir = os.path.join(ROOT, 'baseline', '_ref')
+        if not os.path.exists(os.path.join(ref_dir, 'distributed_dot_product', 'module.py')):
+            if rank == 0:
+                print(json.dumps({'impl': 'reference',
+                                  'unavailable': 'baseline/_ref is missing: run baseline/install_reference.sh'}))
+            return 0
+        # the reference package has the same import name as ours: make it (and the hvd/mpi4py shim) win
+        sys.path[:] = [p for p in sys.path if os.path.abspath(p or '.') != ROOT]
+        sys.path.insert(0, ref_dir)
+        sys.path.insert(0, os.path.join(ROOT, 'baseline', 'shim'))
+    import torch
+    if not torch.cuda.is_available():
+        if rank == 0:
+            print(json.dumps({'impl': args.impl, 'unavailable': 'no CUDA device'}))
+        return 0
+    torch.cuda.set_device(local_rank % torch.cuda.device_count())
+    dev = torch.device('cuda', torch.cuda.current_device())
+    import torch.distributed as dist
+
+    if reference:
+        import horovod.torch as hvd
+        hvd.init()
+        torch.backends.cuda.matmul.allow_tf32 = True
+        torch.backends.cudnn.allow_tf32 = True
+        from distributed_dot_product.module import DistributedDotProductAttn
+        import distributed_dot_product as pkg
+        assert os.path.abspath(pkg.__file__).startswith(os.path.join(ROOT, 'baseline', '_ref')), pkg.__file__
+        dtype = torch.float32
+        count_launches = None
+    else:
+        from distributed_dot_product.utils import comm
+        comm.init()
+        from distributed_dot_product.module import DistributedDotProductAttn
+        from distributed_dot_product import _native
+        _native.load()
+        dtype = {'bf16': torch.bfloat16, 'fp16': torch.float16, 'fp32': torch.float32}[args.dtype]
+        count_launches = _native
+    world = dist.get_world_size() if dist.is_initialized() else 1
+
+    total_t = args.T if args.T else ROWS_PER_GPU * world
+    tn = total_t // world
+    torch.manual_seed(111)
+    model = DistributedDotProductAttn(args.d_model, num_heads=args.heads, offset=args.offset).to(dev, dtype)
+    if world > 1:
+        for p in model.parameters():
+            dist.broadcast(p.data, src=0)
+    torch.manual_seed(222 + rank)
+    # synthetic data: pinned host buffers (e2e path) and resident device copies (device-timed path)
+    x_host = torch.rand(1, tn, args.d_model).to(dtype).pin_memory()
+    y_host = torch.rand(1, tn, args.d_model).to(dtype).pin_memory()
+    x_dev = x_host.to(dev)
+    y_dev = y_host.to(dev)
+    mask = torch.zeros(1, tn, total_t, device=dev).bool()  # the reference example's all-False mask
+    loss_host = torch.zeros(1, dtype=torch.float32).pin_memory()
+
+    def step(x, y):
+        for p in model.parameters():
+            p.grad = None
+        out = model(x, x, x, mask)
+        loss = torch.nn.functional.mse_loss(out.float(), y.float())
+        loss.backward()
+        return loss
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    result = {'impl': args.impl}
+    try:
+        for _ in range(max(args.warmup, 3)):
+            step(x_dev, y_dev)
+        barrier()
+        # ---------------- device-timed region
+        sampler = ClockSampler(physical_gpu_index(local_rank))
+        sampler.start()
+        l0 = count_launches.launch_count if count_launches else 0
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(args.steps):
+            step(x_dev, y_dev)
+        e1.record()
+        barrier()
+        launches = (count_launches.launch_count - l0) if count_launches else None
+        sampler.stop_flag.set()
+        sampler.join()
+        ms = e0.elapsed_time(e1) / args.steps
+        # ---------------- end-to-end region: H2D of the step inputs + D2H of the loss, every step
+        x_in = torch.empty_like(x_dev)
+        y_in = torch.empty_like(y_dev)
+        for _ in range(2):
+            x_in.copy_(x_host, non_blocking=True)
+            y_in.copy_(y_host, non_blocking=True)
+            loss_host.copy_(step(x_in, y_in).detach().reshape(1), non_blocking=True)
+        barrier()
+        e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e2.record()
+        for _ in range(args.steps):
+            x_in.copy_(x_host, non_blocking=True)
+            y_in.copy_(y_host, non_blocking=True)
+            loss = step(x_in, y_in)
+            loss_host.copy_(loss.detach().reshape(1), non_blocking=True)
+            torch.cuda.current_stream().synchronize()  # the caller reads the loss every step
+        e3.record()
+        barrier()
+        ms_e2e = e2.elapsed_time(e3) / args.steps
+        t = torch.tensor([ms, ms_e2e], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms, ms_e2e = t.tolist()
+        h2d = x_host.numel() * x_host.element_size() + y_host.numel() * y_host.element_size()
+        flops_fwd = 4.0 * 2 * tn * args.d_model * args.d_model + 2 * 2.0 * tn * total_t * args.d_model
+        result.update({
+            'metric': 'DistributedDotProductAttn fwd+bwd ms/step (16 heads, d_model=1024, T/N=8192)',
+            'value': ms, 'unit': 'ms', 'n_gpus': world, 'steps': args.steps, 'warmup': max(args.warmup, 3),
+            'ms_per_step': ms, 'higher_is_better': False, 'scaling': 'weak', 'vs_baseline': None,
+            'dtype': 'fp32 storage, tf32 matmul (reference native dtype)' if reference else args.dtype,
+            'data': 'synthetic',
+            'config': {'model': 'DistributedDotProductAttn heads=%d d_model=%d' % (args.heads, args.d_model),
+                       'global_batch': 1, 'seq_len': total_t, 'rows_per_gpu': tn,
+                       'parallelism': 'sp%d (time axis split, all-gather-KV)' % world,
+                       'offset': args.offset,
+                       'l2': 'inputs larger than L2: %.1f GB score slab per GPU per pass'
+                             % (args.heads * tn * total_t * (4 if reference else 2) / 1e9),
+                       'scaling_note': 'rows per GPU fixed; per-GPU attention FLOPs grow with N (T^2/N)'},
+            'tflops_per_gpu': 3.0 * flops_fwd / (ms * 1e-3) / 1e12,
+            'clocks': sampler.summary(),
+            'e2e': {'value': ms_e2e, 'unit': 'ms', 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': 4},
+            'gpu_launches': launches if launches is not None else 0,
+            'loss': float(loss_host.item()),
+        })
+        if reference:
+            result['gpu_launches_note'] = 'reference arm: library kernels only (cuBLAS/ATen/NCCL)'
+    except torch.cuda.OutOfMemoryError as e:
+        result = {'impl': args.impl, 'unavailable': 'CUDA out of memory at T=%d on %d GPU(s): %s'
+                  % (total_t, world, str(e).split('.')[0])}
+    if rank == 0:
+        print(json.dumps(result))
+    if world > 1:
+        try:
+            dist.barrier()
+            if not reference:
+                from distributed_dot_product.utils import comm
+                comm.shutdown()
+            else:
+                dist.destroy_process_group()
+        except Exception:
+            pass
+    return 0
+
+
+if __name__ == '__main__':
+    sys.exit(main())

@@ -21,6 +21,7 @@ LIB_SOURCES = [
     "csrc/runtime/runtime.cu",
     "csrc/gemm/gemm_api.cu",
     "csrc/softmax/softmax.cu",
+    "csrc/reduce/colsum.cu",
 ]
 HEADERS = [
     "include/ddp_b200.h",

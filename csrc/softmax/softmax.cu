@@ -289,24 +289,6 @@ __global__ void rowdot_kernel(const T* a, const T* b, float* out, long long rows
   if (lane == 0) out[r] = s;
 }
 
-// ------------------------------------------------------------------ column sum (bias gradient)
-template <typename T>
-__global__ void colsum_kernel(const T* x, T* out, long long rows, int cols, long long ld) {
-  __shared__ float part[8][33];
-  const int c = blockIdx.x * 32 + threadIdx.x;
-  float s = 0.f;
-  if (c < cols)
-    for (long long r = threadIdx.y; r < rows; r += 8) s += to_f(x[r * ld + c]);
-  part[threadIdx.y][threadIdx.x] = s;
-  __syncthreads();
-  if (threadIdx.y == 0 && c < cols) {
-    float t = 0.f;
-#pragma unroll
-    for (int i = 0; i < 8; ++i) t += part[i][threadIdx.x];
-    out[c] = from_f<T>(t);
-  }
-}
-
 static bool aligned16(const void* p, long long ld, long long sb0, long long sb1, int es) {
   return (reinterpret_cast<uintptr_t>(p) & 15) == 0 && (ld * es) % 16 == 0 && (sb0 * es) % 16 == 0 && (sb1 * es) % 16 == 0;
 }
@@ -429,16 +411,4 @@ extern "C" int ddp_rowdot(const ddp_tensor* a, const ddp_tensor* b, float* out, 
       rowdot_kernel<__half><<<grid, wpb * 32, 0, st>>>((const __half*)a->ptr, (const __half*)b->ptr, out, rows, (int)a->cols, a->ld, b->ld);
   }
   return cuda_check(cudaGetLastError(), "rowdot launch");
-}
-
-extern "C" int ddp_colsum(const ddp_tensor* x, void* out, void* stream) {
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
-  const dim3 block(32, 8);
-  const unsigned grid = (unsigned)((x->cols + 31) / 32);
-  switch (x->dtype) {
-    case DDP_F32: colsum_kernel<float><<<grid, block, 0, st>>>((const float*)x->ptr, (float*)out, x->rows, (int)x->cols, x->ld); break;
-    case DDP_BF16: colsum_kernel<__nv_bfloat16><<<grid, block, 0, st>>>((const __nv_bfloat16*)x->ptr, (__nv_bfloat16*)out, x->rows, (int)x->cols, x->ld); break;
-    default: colsum_kernel<__half><<<grid, block, 0, st>>>((const __half*)x->ptr, (__half*)out, x->rows, (int)x->cols, x->ld);
-  }
-  return cuda_check(cudaGetLastError(), "colsum launch");
 }

@@ -63,7 +63,7 @@ def _gpu(t):
 
 
 def _gemm(op, left, right, offset, out=None, alpha=1.0):
-    from distributed_dot_product.ops import gemm as _g
+    import distributed_dot_product.ops.gemm as _g
     return _g.gemm(op, left, right, offset=offset, out=out, alpha=alpha)
 
 

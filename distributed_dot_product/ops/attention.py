@@ -15,7 +15,7 @@ the gradient slab reuses one buffer for ``dP`` and ``dS``.
 import torch
 
 from distributed_dot_product import _native
-from distributed_dot_product.ops import gemm as _g
+import distributed_dot_product.ops.gemm as _g
 from distributed_dot_product.ops.softmax import softmax_backward, softmax_forward
 
 

@@ -13,15 +13,20 @@ import torch
 import torch.nn.functional as F
 
 from distributed_dot_product import _native
-from distributed_dot_product.ops import gemm as _g
+import distributed_dot_product.ops.gemm as _g
 
 
-def _colsum(x2):
+def colsum(x2):
+    """Column sum of a 2-D CUDA tensor (row-split two-stage reduction through an fp32 scratch buffer)."""
     lib = _native.load()
     out = torch.empty(x2.size(-1), dtype=x2.dtype, device=x2.device)
     v = _g.as_view(x2.unsqueeze(0).unsqueeze(0))
-    _native.check(lib.ddp_colsum(ctypes.byref(v), ctypes.c_void_p(out.data_ptr()), _g._stream()))
-    _native.count_launch()
+    nbytes = lib.ddp_colsum_scratch_bytes(x2.size(0), x2.size(1))
+    scratch = torch.empty(nbytes, dtype=torch.uint8, device=x2.device) if nbytes else None
+    _native.check(lib.ddp_colsum(ctypes.byref(v), ctypes.c_void_p(out.data_ptr()),
+                                 ctypes.c_void_p(scratch.data_ptr()) if scratch is not None else None,
+                                 nbytes, _g._stream()))
+    _native.count_launch(2 if nbytes else 1)
     return out
 
 
@@ -46,7 +51,7 @@ class _Linear(torch.autograd.Function):
             gw = _g.gemm(_native.OP_TN, g2, x2, distributed=False)
         if ctx.has_bias and ctx.needs_input_grad[2]:
             g2c = g2 if g2.stride(-1) == 1 else g2.contiguous()
-            gb = _colsum(g2c)
+            gb = colsum(g2c)
         return gx, gw, gb
 
 

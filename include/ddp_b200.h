@@ -85,8 +85,12 @@ int ddp_softmax_bwd(const ddp_tensor* y, const ddp_tensor* dy, const ddp_tensor*
 /* out[r] = sum_c a[r][c] * b[r][c] in fp32; a, b are [rows][cols] views (row strides ld). */
 int ddp_rowdot(const ddp_tensor* a, const ddp_tensor* b, float* out, void* stream);
 
-/* out[c] = sum_r x[r][c]  (bias gradient).  x is [rows][cols] with row stride ld; out has x's dtype. */
-int ddp_colsum(const ddp_tensor* x, void* out, void* stream);
+/* out[c] = sum_r x[r][c]  (bias gradient; autograd of module.py:43-45,75 with add_bias=True).  x is
+ * [rows][cols] with row stride ld; out has x's dtype.  `scratch` is caller-provided device memory of
+ * `scratch_bytes` bytes (ddp_colsum_scratch_bytes gives the useful size) holding fp32 partial sums of the
+ * row-split first stage; it may be NULL, then one CTA per 32 columns walks all the rows. */
+size_t ddp_colsum_scratch_bytes(int64_t rows, int64_t cols);
+int ddp_colsum(const ddp_tensor* x, void* out, void* scratch, size_t scratch_bytes, void* stream);
 
 /* ---- symmetric heap (runtime) ------------------------------------------------------------ */
 /* Allocates `bytes` of device memory suitable for peer mapping and returns a 64-byte IPC handle. */

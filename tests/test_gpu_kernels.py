@@ -1,0 +1,222 @@
+# -*- coding: utf-8 -*-
+"""Numerics of every sm_100a kernel against a plain PyTorch fp32 reference of the same op (one GPU)."""
+import math
+import os
+import subprocess
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _tol(dtype):
+    return {torch.float32: (2e-3, 2e-3), torch.bfloat16: (2e-2, 2e-2), torch.float16: (4e-3, 4e-3)}[dtype]
+
+
+def _close(got, want, dtype, scale=1.0):
+    rtol, atol = _tol(dtype)
+    got, want = got.float(), want.float()
+    err = (got - want).abs().max().item()
+    bound = atol * scale + rtol * want.abs().max().item()
+    assert err <= bound, 'max abs err %g > %g' % (err, bound)
+
+
+def test_native_library_loads(cuda_device):
+    from distributed_dot_product import _native
+    lib = _native.load()
+    assert lib.ddp_version() >= 100
+    assert lib.ddp_num_sms() > 0
+    maps = open('/proc/self/maps').read()
+    assert 'libddp_b200.so' in maps
+
+
+@pytest.mark.parametrize('dtype', [torch.bfloat16, torch.float16, torch.float32])
+@pytest.mark.parametrize('shape', [((), 128, 64), ((2,), 200, 96), ((2, 3), 77, 40), ((1, 4), 300, 264)])
+def test_products_world1(cuda_device, dtype, shape):
+    from distributed_dot_product.multiplication.functions import (
+        distributed_matmul_all, distributed_matmul_nt, distributed_matmul_tn)
+    lead, t, d = shape
+    torch.manual_seed(0)
+    a = torch.randn(*lead, t, d, device=cuda_device).to(dtype)
+    b = torch.randn(*lead, t, d, device=cuda_device).to(dtype)
+    s = torch.randn(*lead, t, t, device=cuda_device).to(dtype)
+    k = math.sqrt(d)
+    _close(distributed_matmul_nt(a, b, offset=32), a.float() @ b.float().transpose(-1, -2), dtype, scale=k)
+    _close(distributed_matmul_all(s, b, offset=32), s.float() @ b.float(), dtype, scale=math.sqrt(t))
+    _close(distributed_matmul_tn(s, b), s.float().transpose(-1, -2) @ b.float(), dtype, scale=math.sqrt(t))
+    assert distributed_matmul_nt(a, b).dtype == dtype and distributed_matmul_nt(a, b).shape == (*lead, t, t)
+
+
+def test_products_exact_small_integers(cuda_device):
+    """Integers exactly representable in bf16/tf32 with fp32 accumulation -> bitwise equality."""
+    from distributed_dot_product.multiplication.functions import (
+        distributed_matmul_all, distributed_matmul_nt, distributed_matmul_tn)
+    g = torch.Generator(device='cpu').manual_seed(3)
+    for dtype in (torch.float32, torch.bfloat16):
+        a = torch.randint(-3, 4, (2, 2, 150, 24), generator=g).to(cuda_device, dtype)
+        b = torch.randint(-3, 4, (2, 2, 150, 24), generator=g).to(cuda_device, dtype)
+        s = torch.randint(-1, 2, (2, 2, 150, 150), generator=g).to(cuda_device, dtype)
+        assert (distributed_matmul_nt(a, b).float() == a.float() @ b.float().transpose(-1, -2)).all()
+        assert (distributed_matmul_all(s, b).float() == s.float() @ b.float()).all()
+        assert (distributed_matmul_tn(s, b).float() == s.float().transpose(-1, -2) @ b.float()).all()
+
+
+def test_products_unaligned_and_strided_views(cuda_device):
+    from distributed_dot_product.multiplication.functions import (
+        distributed_matmul_all, distributed_matmul_nt, distributed_matmul_tn)
+    torch.manual_seed(1)
+    # reference test shape: LENGTH=4, DIM=6 (rows of 12 / 24 bytes: not TMA addressable -> padded staging copy)
+    a = torch.randn(1, 4, 6, device=cuda_device)
+    b = torch.randn(1, 4, 6, device=cuda_device)
+    s = torch.randn(1, 4, 4, device=cuda_device)
+    _close(distributed_matmul_nt(a, b, offset=2), a @ b.transpose(-1, -2), torch.float32, 3)
+    _close(distributed_matmul_all(s, b, offset=2), s @ b, torch.float32, 3)
+    _close(distributed_matmul_tn(s, b), s.transpose(-1, -2) @ b, torch.float32, 3)
+    # head-split views of a [B, T, H*d] projection go straight into the tensor maps
+    x = torch.randn(2, 70, 4 * 32, device=cuda_device).bfloat16()
+    y = torch.randn(2, 70, 4 * 32, device=cuda_device).bfloat16()
+    xv = x.view(2, 70, 4, 32).transpose(1, 2)
+    yv = y.view(2, 70, 4, 32).transpose(1, 2)
+    _close(distributed_matmul_nt(xv, yv), xv.float() @ yv.float().transpose(-1, -2), torch.bfloat16, 6)
+    # int64 / float64 inputs are computed on the tensor cores in fp32 and cast back
+    ai = torch.arange(4 * 6, device=cuda_device).view(1, 4, 6)
+    assert (distributed_matmul_nt(ai, ai, offset=2).cpu() == ai.cpu() @ ai.cpu().transpose(-1, -2)).all()
+
+
+@pytest.mark.parametrize('dtype', [torch.bfloat16, torch.float32])
+@pytest.mark.parametrize('cols', [64, 1000, 5000, 40000])
+def test_masked_softmax_fwd_bwd(cuda_device, dtype, cols):
+    from distributed_dot_product.ops.softmax import masked_softmax, masked_softmax_
+    torch.manual_seed(2)
+    b, h, rows = 2, 3, 5
+    x = (torch.randn(b, h, rows, cols, device=cuda_device) * 3).to(dtype)
+    mask = torch.rand(b, rows, cols, device=cuda_device) < 0.3
+    mask[..., 0] = False
+    scale = 0.37
+    xr = x.float().requires_grad_(True)
+    ref = torch.softmax((xr * scale).masked_fill(mask.unsqueeze(1), -float('inf')), dim=-1)
+    g = torch.randn_like(ref)
+    ref.backward(g)
+    xt = x.clone().requires_grad_(True)
+    out = masked_softmax(xt, mask, scale)
+    out.backward(g.to(dtype))
+    tol = 1e-5 if dtype == torch.float32 else 8e-3
+    assert (out.float() - ref).abs().max().item() < tol
+    assert (xt.grad.float() - xr.grad).abs().max().item() < tol * 4
+    # in place, no mask
+    y = masked_softmax_(x.clone(), None, scale)
+    assert (y.float() - torch.softmax(x.float() * scale, -1)).abs().max().item() < tol
+    # row sums
+    assert (out.float().sum(-1) - 1).abs().max().item() < (1e-4 if dtype == torch.float32 else 2e-2)
+
+
+def test_masked_softmax_unaligned_and_nan_row(cuda_device):
+    from distributed_dot_product.ops.softmax import masked_softmax
+    x = torch.randn(1, 2, 3, 37, device=cuda_device)
+    mask = torch.zeros(1, 3, 37, dtype=torch.bool, device=cuda_device)
+    mask[0, 1] = True
+    out = masked_softmax(x, mask, 1.0)
+    ref = torch.softmax(x.masked_fill(mask.unsqueeze(1), -float('inf')), -1)
+    assert torch.isnan(out[0, :, 1]).all()
+    assert torch.allclose(out[0, :, 0], ref[0, :, 0], atol=1e-6)
+
+
+@pytest.mark.parametrize('dtype', [torch.bfloat16, torch.float32])
+@pytest.mark.parametrize('bias', [False, True])
+def test_linear_fwd_bwd(cuda_device, dtype, bias):
+    from distributed_dot_product.ops.linear import linear
+    torch.manual_seed(4)
+    x = torch.randn(2, 90, 72, device=cuda_device).to(dtype).requires_grad_(True)
+    w = (torch.randn(40, 72, device=cuda_device) / 8).to(dtype).requires_grad_(True)
+    bb = torch.randn(40, device=cuda_device).to(dtype).requires_grad_(True) if bias else None
+    y = linear(x, w, bb)
+    g = torch.randn_like(y)
+    y.backward(g)
+    xr, wr = x.detach().float().requires_grad_(True), w.detach().float().requires_grad_(True)
+    br = bb.detach().float().requires_grad_(True) if bias else None
+    yr = torch.nn.functional.linear(xr, wr, br)
+    yr.backward(g.float())
+    _close(y, yr, dtype, 2)
+    _close(x.grad, xr.grad, dtype, 2)
+    _close(w.grad, wr.grad, dtype, 14)
+    if bias:
+        _close(bb.grad, br.grad, dtype, 14)
+
+
+@pytest.mark.parametrize('dtype,heads,bias', [(torch.float32, 1, False), (torch.float32, 4, True),
+                                              (torch.bfloat16, 4, False)])
+def test_module_vs_dense_twin_world1(cuda_device, dtype, heads, bias):
+    """Reference recipe (tests/test_gradient.py) on one GPU: native path vs the torch-composed oracle."""
+    from distributed_dot_product.module import DistributedDotProductAttn
+    torch.manual_seed(5)
+    dim, t = 256, 144
+    model = DistributedDotProductAttn(dim, num_heads=heads, add_bias=bias).to(cuda_device, dtype)
+    twin = DistributedDotProductAttn(dim, num_heads=heads, add_bias=bias, distributed=False).to(cuda_device).float()
+    twin.load_state_dict({k: v.float() for k, v in model.state_dict().items()})
+    k = torch.rand(1, t, dim, device=cuda_device).to(dtype).requires_grad_(True)
+    q = torch.rand(1, t, dim, device=cuda_device).to(dtype).requires_grad_(True)
+    mask = torch.triu(torch.ones(t, t, dtype=torch.bool, device=cuda_device), diagonal=1).unsqueeze(0)
+    out = model(k, q, k, mask)
+    out.float().sum().backward()
+    kr, qr = k.detach().float().requires_grad_(True), q.detach().float().requires_grad_(True)
+    ref = twin(kr, qr, kr, mask)
+    ref.sum().backward()
+    tol = 3e-3 if dtype == torch.float32 else 4e-2
+    assert (out.float() - ref).abs().max().item() < tol
+    assert (k.grad.float() - kr.grad).abs().max().item() < tol * 4
+    assert (q.grad.float() - qr.grad).abs().max().item() < tol * 4
+    for (n, p), (_, pr) in zip(model.named_parameters(), twin.named_parameters()):
+        rel = (p.grad.float() - pr.grad).abs().max().item() / (pr.grad.abs().max().item() + 1e-6)
+        assert rel < (2e-2 if dtype == torch.float32 else 6e-2), (n, rel)
+
+
+def test_autograd_ops_world1(cuda_device):
+    from distributed_dot_product.multiplication.ops import (
+        FullMultiplication, LeftTransposeMultiplication, RightTransposeMultiplication)
+    torch.manual_seed(6)
+    t, d = 96, 40
+    a = torch.randn(2, t, d, device=cuda_device, requires_grad=True)
+    b = torch.randn(2, t, d, device=cuda_device, requires_grad=True)
+    s = torch.randn(2, t, t, device=cuda_device, requires_grad=True)
+    for op, l, r, dense in ((RightTransposeMultiplication, a, b, lambda x, y: x @ y.transpose(-1, -2)),
+                            (FullMultiplication, s, b, lambda x, y: x @ y),
+                            (LeftTransposeMultiplication, s, b, lambda x, y: x.transpose(-1, -2) @ y)):
+        l1, r1 = l.detach().clone().requires_grad_(True), r.detach().clone().requires_grad_(True)
+        out = op.apply(l1, r1, 32)
+        g = torch.randn_like(out)
+        out.backward(g)
+        l2, r2 = l.detach().clone().requires_grad_(True), r.detach().clone().requires_grad_(True)
+        ref = dense(l2, r2)
+        ref.backward(g)
+        _close(out, ref, torch.float32, 10)
+        _close(l1.grad, l2.grad, torch.float32, 10)
+        _close(r1.grad, r2.grad, torch.float32, 10)
+
+
+def test_cuda_harness_emulated_ranks(cuda_device):
+    """The standalone CUDA harness validates the fused collective paths with emulated ranks on one GPU
+    (produce phase of every rank, then consume phase) - see csrc/tests/gemm_harness.cu."""
+    exe = os.path.join(ROOT, 'build', 'gemm_harness')
+    if not os.path.exists(exe):
+        subprocess.check_call(['python', os.path.join(ROOT, 'build.py'), 'harness'], cwd=ROOT)
+    r = subprocess.run([exe, 'quick'], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
+    tail = '\n'.join(r.stdout.splitlines()[-15:])
+    assert r.returncode == 0, tail
+    assert 'fail=0' in r.stdout, tail
+
+
+@pytest.mark.parametrize('dtype', [torch.bfloat16, torch.float32])
+@pytest.mark.parametrize('rows,cols', [(8192, 1024), (3000, 40), (100, 264)])
+def test_colsum_row_split(cuda_device, dtype, rows, cols):
+    """Bias-gradient column sum: the row-split two-stage kernel (fp32 partials in scratch) vs torch."""
+    from distributed_dot_product.ops.linear import colsum
+    torch.manual_seed(8)
+    x = torch.randn(rows, cols, device=cuda_device).to(dtype)
+    got = colsum(x)
+    want = x.float().sum(0)
+    tol = 1e-3 if dtype == torch.float32 else 1.0
+    assert got.dtype == dtype
+    assert (got.float() - want).abs().max().item() <= tol * max(1.0, want.abs().max().item() / 64)
