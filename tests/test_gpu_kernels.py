@@ -96,11 +96,11 @@ def test_masked_softmax_fwd_bwd(cuda_device, dtype, cols):
     mask = torch.rand(b, rows, cols, device=cuda_device) < 0.3
     mask[..., 0] = False
     scale = 0.37
-    xr = x.float().requires_grad_(True)
+    xr = x.detach().float().clone().requires_grad_(True)
     ref = torch.softmax((xr * scale).masked_fill(mask.unsqueeze(1), -float('inf')), dim=-1)
     g = torch.randn_like(ref)
     ref.backward(g)
-    xt = x.clone().requires_grad_(True)
+    xt = x.detach().clone().requires_grad_(True)
     out = masked_softmax(xt, mask, scale)
     out.backward(g.to(dtype))
     tol = 1e-5 if dtype == torch.float32 else 8e-3
@@ -168,8 +168,11 @@ def test_module_vs_dense_twin_world1(cuda_device, dtype, heads, bias):
     assert (out.float() - ref).abs().max().item() < tol
     assert (k.grad.float() - kr.grad).abs().max().item() < tol * 4
     assert (q.grad.float() - qr.grad).abs().max().item() < tol * 4
+    # the queries bias shifts every score of a row equally, so its true gradient is ~0: judge every
+    # parameter against the layer-wide gradient scale, not its own
+    gscale = max(pr.grad.abs().max().item() for pr in twin.parameters())
     for (n, p), (_, pr) in zip(model.named_parameters(), twin.named_parameters()):
-        rel = (p.grad.float() - pr.grad).abs().max().item() / (pr.grad.abs().max().item() + 1e-6)
+        rel = (p.grad.float() - pr.grad).abs().max().item() / max(pr.grad.abs().max().item(), 0.05 * gscale)
         assert rel < (2e-2 if dtype == torch.float32 else 6e-2), (n, rel)
 
 
