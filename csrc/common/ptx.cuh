@@ -175,11 +175,26 @@ __device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t* p) {
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
   asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
-// Spin until *p >= want (wrap-safe signed distance).
-__device__ __forceinline__ void wait_flag_ge(const uint32_t* p, uint32_t want) {
+__device__ __forceinline__ uint64_t global_timer_ns() {
+  uint64_t t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+// Spin until *p >= want (wrap-safe signed distance).  A peer that never shows up must not hang the GPU:
+// after `timeout_ns` the wait gives up, records `code` in *status (if non-null) and returns false; the caller
+// carries on (its results are then invalid and the host raises when it reads the status word).
+__device__ __forceinline__ bool wait_flag_ge(const uint32_t* p, uint32_t want, uint32_t* status = nullptr,
+                                             uint32_t code = 1, uint64_t timeout_ns = 20000000000ull) {
+  if (static_cast<int32_t>(ld_acquire_sys(p) - want) >= 0) return true;
+  const uint64_t t0 = global_timer_ns();
   while (static_cast<int32_t>(ld_acquire_sys(p) - want) < 0) {
     __nanosleep(64);
+    if (global_timer_ns() - t0 > timeout_ns) {
+      if (status) atomicMax(status, code);
+      return false;
+    }
   }
+  return true;
 }
 
 // 16-byte streaming global accesses.

@@ -270,6 +270,7 @@ extern "C" int ddp_gemm(int op, const ddp_tensor* A, const ddp_tensor* B, const 
       p.done[i] = comm->done[i];
     }
     p.exit_counter = comm->exit_counter;
+    p.status = comm->status;
   } else {
     p.phase_mask = 3; p.chunk_rows = 1 << 30; p.n_chunks = 1;
   }

@@ -46,6 +46,7 @@ struct alignas(64) GemmKParams {
   uint32_t* flags[DDP_MAX_WORLD];
   uint32_t* done[DDP_MAX_WORLD];
   uint32_t* exit_counter;
+  uint32_t* status;  // sticky error word in local memory (0 = ok; 1..5 = which wait timed out)
   // all-gather push source (the local `right` operand), byte strides
   const char* push_src;
   long long push_ld, push_sb0, push_sb1;
@@ -243,7 +244,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
           const int hi_row = min(n0 + BN, p.N) - 1;
           const int c_hi = hi_row / p.chunk_rows;
           for (int c = c_lo; c <= c_hi; ++c)
-            wait_flag_ge(my_flags + (static_cast<size_t>(tc.seg) * Bt + tc.b) * p.n_chunks + c, p.seq);
+            wait_flag_ge(my_flags + (static_cast<size_t>(tc.seg) * Bt + tc.b) * p.n_chunks + c, p.seq, p.status, 1);
           fence_proxy_async();
         }
         int waited_seg = -1, waited_chunk = -1;
@@ -264,7 +265,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
             }
             if (c_hi > waited_chunk) {
               for (int c = max(c_lo, waited_chunk + 1); c <= c_hi; ++c)
-                wait_flag_ge(my_flags + (static_cast<size_t>(seg) * Bt + tc.b) * p.n_chunks + c, p.seq);
+                wait_flag_ge(my_flags + (static_cast<size_t>(seg) * Bt + tc.b) * p.n_chunks + c, p.seq, p.status, 2);
               waited_chunk = c_hi;
               fence_proxy_async();
             }
@@ -357,7 +358,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
         // The peers must have finished call seq-2 before we overwrite this parity of their workspace.
         if (lane > 0 && lane < p.world) {
           const int q = (p.rank + lane) % p.world;
-          wait_flag_ge(p.done[p.rank] + q, p.seq - 2u);
+          wait_flag_ge(p.done[p.rank] + q, p.seq - 2u, p.status, 3);
         }
         __syncwarp();
       }
@@ -417,7 +418,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
       const int rows_valid = max(0, min(32, p.M - row0));
       const bool tn_remote = (OP == DDP_OP_TN) && dist;
       if (tn_remote && tc.seg != p.rank && !(done_ok & (1u << tc.seg))) {
-        if (lane == 0) wait_flag_ge(p.done[p.rank] + tc.seg, p.seq - 2u);
+        if (lane == 0) wait_flag_ge(p.done[p.rank] + tc.seg, p.seq - 2u, p.status, 4);
         __syncwarp();
         done_ok |= 1u << tc.seg;
       }
@@ -489,7 +490,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
         const int b = r / p.m_blocks;
         if (lane < p.world) {
           const size_t fidx = (((static_cast<size_t>(lane) * Bt + b) * p.m_blocks + mb) * p.n_blocks + nb) * 4 + quad;
-          wait_flag_ge(my_flags + fidx, p.seq);
+          wait_flag_ge(my_flags + fidx, p.seq, p.status, 5);
         }
         __syncwarp();
         const int b1i = b / p.b0, b0i = b - b1i * p.b0;

@@ -29,7 +29,8 @@ class Comm(ctypes.Structure):
     _fields_ = [('world', ctypes.c_int32), ('rank', ctypes.c_int32), ('seq', ctypes.c_uint32),
                 ('phase_mask', ctypes.c_int32), ('chunk_rows', ctypes.c_int32), ('_pad', ctypes.c_int32),
                 ('ws', ctypes.c_void_p * MAX_WORLD), ('flags', ctypes.c_void_p * MAX_WORLD),
-                ('done', ctypes.c_void_p * MAX_WORLD), ('exit_counter', ctypes.c_void_p)]
+                ('done', ctypes.c_void_p * MAX_WORLD), ('exit_counter', ctypes.c_void_p),
+                ('status', ctypes.c_void_p)]
 
 
 class NativeError(RuntimeError):

@@ -197,6 +197,7 @@ class _Heap(object):
                 cm.flags[r] = self.peers[r] + off + new_ws
                 cm.done[r] = self.peers[r]
             cm.exit_counter = self.base + 256
+            cm.status = self.base + 384
             self.comm[parity] = cm
 
     def next_comm(self, chunk_rows):

@@ -51,6 +51,8 @@ typedef struct ddp_comm {
   uint32_t* flags[DDP_MAX_WORLD];
   uint32_t* done[DDP_MAX_WORLD]; /* done[r][q] = last seq rank q finished, stored in rank r's memory */
   uint32_t* exit_counter;        /* one zero-initialised uint32 in local memory */
+  uint32_t* status;              /* sticky error word in local memory (0 = ok); a wait on a peer that
+                                    exceeds 20 s stores which wait (1..5) here instead of hanging; may be NULL */
 } ddp_comm;
 
 const char* ddp_last_error(void);

@@ -66,9 +66,13 @@ def _module(rank, world):
     kg, qg = gather(k).requires_grad_(True), gather(q).requires_grad_(True)
     ref = twin(kg, qg, kg, gmask)
     ref.sum().backward()
-    assert (out - ref[:, rows]).abs().max().item() < 3e-3
-    assert (k.grad - kg.grad[:, rows]).abs().max().item() < 1e-2
-    assert (q.grad - qg.grad[:, rows]).abs().max().item() < 1e-2
+    def rel(a, b):
+        return (a - b).abs().max().item() / (b.abs().max().item() + 1e-12)
+
+    # fp32 tensors run TF32 tensor-core math (10-bit mantissa) through six chained products
+    errs = {'out': rel(out, ref[:, rows]), 'k.grad': rel(k.grad, kg.grad[:, rows]),
+            'q.grad': rel(q.grad, qg.grad[:, rows])}
+    assert all(v < 1e-2 for v in errs.values()), errs
     allreduce_gradients(model)
     gscale = max(pr.grad.abs().max().item() for pr in twin.parameters())
     for (n, p), (_, pr) in zip(model.named_parameters(), twin.named_parameters()):
@@ -80,11 +84,11 @@ def _module(rank, world):
 def test_fused_products_multi_gpu(world):
     if _ngpu() < world:
         pytest.skip('needs %d GPUs' % world)
-    run_distributed(_products, world, use_cuda=True)
+    run_distributed(_products, world, use_cuda=True, timeout=150)
 
 
 @pytest.mark.parametrize('world', [2, 8])
 def test_module_multi_gpu(world):
     if _ngpu() < world:
         pytest.skip('needs %d GPUs' % world)
-    run_distributed(_module, world, use_cuda=True)
+    run_distributed(_module, world, use_cuda=True, timeout=150)
