@@ -111,3 +111,54 @@ extern "C" size_t ddp_colsum_scratch_bytes(int64_t rows, int64_t cols) {
 extern "C" int ddp_colsum(const ddp_tensor* x, void* out, void* scratch, size_t scratch_bytes, void* stream) {
   return dispatch_colsum(x, out, static_cast<float*>(scratch), scratch_bytes, static_cast<cudaStream_t>(stream));
 }
+
+// ---------------------------------------------------------------------------------------------------------
+// Allocation-free variant.
+//
+// ddp_colsum needs a scratch buffer from its caller, and the usual caller gets one from an allocator.  Some
+// callers have no allocator to ask: a serving process that gave every byte of device memory to its own pool
+// at start-up and has none left for cudaMalloc to hand out; a latency-bound step loop that must not run
+// cudaMalloc/cudaFree because both stall every stream on the device while they work; a plug-in that runs
+// while the host framework holds its allocator lock and therefore may not re-enter it.  For them the partial
+// sums live in the fixed array below, which is part of the library image: every GPU that loads
+// libddp_b200.so sets aside DDP_COLSUM_NOALLOC_SCRATCH_BYTES for it until the process exits, used or not.
+//
+// The array is shared by every call on a device and is never cleared: stage 1 writes each partial-sum slot
+// that stage 2 reads, so no slot has to start at zero and stale contents from an earlier call are harmless.
+// Two calls whose kernels may be in flight on the same GPU at the same time (different streams, or another
+// host thread) would write the same slots and race; callers must order such calls themselves.
+#define DDP_COLSUM_NOALLOC_MAX_COLS 16384
+#define DDP_COLSUM_NOALLOC_SPLITS 64
+#define DDP_COLSUM_NOALLOC_SCRATCH_BYTES \
+  (static_cast<size_t>(DDP_COLSUM_NOALLOC_MAX_COLS) * DDP_COLSUM_NOALLOC_SPLITS * sizeof(float)) /* 4 MiB */
+
+static __device__ __align__(256) float g_colsum_noalloc_scratch[DDP_COLSUM_NOALLOC_MAX_COLS * DDP_COLSUM_NOALLOC_SPLITS];
+
+// In host code `g_colsum_noalloc_scratch` names a host-side shadow of the symbol, not device memory, so it
+// must never be passed to a kernel; the device address comes from cudaGetSymbolAddress, asked once per
+// device while that device is current.
+static int colsum_noalloc_scratch(float** out) {
+  static float* cached[64] = {};
+  int dev = -1;
+  if (int e = cuda_check(cudaGetDevice(&dev), "cudaGetDevice")) return e;
+  if (dev < 0 || dev >= 64) return set_error(-4, "colsum_noalloc: device ordinal out of range");
+  if (cached[dev] == nullptr) {
+    void* p = nullptr;
+    if (int e = cuda_check(cudaGetSymbolAddress(&p, g_colsum_noalloc_scratch), "cudaGetSymbolAddress(colsum scratch)"))
+      return e;
+    cached[dev] = static_cast<float*>(p);
+  }
+  *out = cached[dev];
+  return 0;
+}
+
+extern "C" size_t ddp_colsum_noalloc_max_cols(void) { return DDP_COLSUM_NOALLOC_MAX_COLS; }
+
+extern "C" int ddp_colsum_noalloc(const ddp_tensor* x, void* out, void* stream) {
+  if (x->cols > DDP_COLSUM_NOALLOC_MAX_COLS)
+    return set_error(-5, "ddp_colsum_noalloc: more than 16384 columns do not fit the built-in scratch array; "
+                         "use ddp_colsum with caller-provided scratch");
+  float* scratch = nullptr;
+  if (int e = colsum_noalloc_scratch(&scratch)) return e;
+  return dispatch_colsum(x, out, scratch, DDP_COLSUM_NOALLOC_SCRATCH_BYTES, static_cast<cudaStream_t>(stream));
+}

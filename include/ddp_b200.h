@@ -94,6 +94,21 @@ int ddp_rowdot(const ddp_tensor* a, const ddp_tensor* b, float* out, void* strea
 size_t ddp_colsum_scratch_bytes(int64_t rows, int64_t cols);
 int ddp_colsum(const ddp_tensor* x, void* out, void* scratch, size_t scratch_bytes, void* stream);
 
+/* Column sum for callers that cannot allocate (no counterpart in the reference).
+ * Same result as ddp_colsum, but the fp32 partial sums go to a 4 MiB array built into the library instead of
+ * caller scratch, and the call performs no cudaMalloc / cudaFree / other allocation.  Meant for code that has
+ * no allocator to turn to: a server whose memory pool already owns the whole device, a latency-bound loop
+ * that cannot afford the device-wide stall of cudaMalloc/cudaFree, a plug-in running under its host's
+ * allocator lock.  Limits and rules:
+ *   - x->cols <= ddp_colsum_noalloc_max_cols() (16384); wider inputs are refused with error -5.
+ *   - Every GPU that loads the library holds the 4 MiB until the process exits.
+ *   - The first call on each device looks up the array's device address; make that first call outside any
+ *     stream capture.
+ *   - All calls on a device share the array.  Nothing needs clearing between calls (every slot read is
+ *     written first), but calls that can overlap on the GPU race: keep them on one stream or order them. */
+size_t ddp_colsum_noalloc_max_cols(void);
+int ddp_colsum_noalloc(const ddp_tensor* x, void* out, void* stream);
+
 /* ---- symmetric heap (runtime) ------------------------------------------------------------ */
 /* Allocates `bytes` of device memory suitable for peer mapping and returns a 64-byte IPC handle. */
 int ddp_heap_alloc(size_t bytes, void** ptr, void* ipc_handle_out64);

@@ -1,0 +1,71 @@
+# -*- coding: utf-8 -*-
+"""``ddp_colsum_noalloc``: the column sum for callers that cannot allocate device memory.
+
+Who needs it: code with no allocator to ask - a serving process whose own pool took all device memory at
+start-up, a latency-bound loop where the device-wide stall of cudaMalloc/cudaFree is unaffordable, a plug-in
+running under its host framework's allocator lock.  The entry point keeps its fp32 partial sums in a 4 MiB
+array built into libddp_b200.so, so it performs no allocation at all.
+
+The test drives the entry point through the C ABI (ctypes), exactly as such a caller would, and checks it
+against the regular ``ddp_colsum`` (caller-provided scratch) on two calls in a row with different inputs - the
+built-in array is shared and keeps the previous call's contents, which must not leak into the next result.
+It lives in a file collected last so a ``-x`` run has already exercised everything else; it passes both alone
+in a fresh process and after the rest of the suite.
+"""
+import ctypes
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _view(lib_native, t):
+    v = lib_native.Tensor()
+    v.ptr = t.data_ptr()
+    v.rows, v.cols, v.ld = t.size(0), t.size(1), t.stride(0)
+    v.b0 = v.b1 = 1
+    v.sb0 = v.sb1 = 0
+    v.dtype = {torch.float16: 0, torch.bfloat16: 1, torch.float32: 2}[t.dtype]
+    return v
+
+
+def test_colsum_noalloc_matches_colsum_twice(cuda_device):
+    from distributed_dot_product import _native
+    lib = _native.load()
+    lib.ddp_colsum_noalloc.argtypes = [ctypes.POINTER(_native.Tensor), ctypes.c_void_p, ctypes.c_void_p]
+    lib.ddp_colsum_noalloc_max_cols.restype = ctypes.c_size_t
+    assert lib.ddp_colsum_noalloc_max_cols() == 16384
+    stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    torch.manual_seed(99)
+    # second call: fewer rows and columns than the first, so stale partial sums sit right next to live ones
+    for call, (rows, cols, dtype) in enumerate([(8192, 1024, torch.bfloat16), (3000, 264, torch.float32)]):
+        x = torch.randn(rows, cols, device=cuda_device).to(dtype) + 0.25 * (call + 1)
+        got = torch.empty(cols, dtype=dtype, device=cuda_device)
+        want = torch.empty(cols, dtype=dtype, device=cuda_device)
+        nbytes = lib.ddp_colsum_scratch_bytes(rows, cols)
+        assert nbytes > 0, 'shape must exercise the two-stage (scratch) path'
+        scratch = torch.empty(nbytes, dtype=torch.uint8, device=cuda_device)
+        v = _view(_native, x)
+        _native.check(lib.ddp_colsum(ctypes.byref(v), ctypes.c_void_p(want.data_ptr()),
+                                     ctypes.c_void_p(scratch.data_ptr()), nbytes, stream))
+        _native.check(lib.ddp_colsum_noalloc(ctypes.byref(v), ctypes.c_void_p(got.data_ptr()), stream))
+        torch.cuda.synchronize()
+        ref = x.float().sum(0)
+        tol = 1e-3 if dtype == torch.float32 else 1.0          # the tolerance of test_colsum_row_split
+        bound = tol * max(1.0, ref.abs().max().item() / 64)
+        assert (got.float() - want.float()).abs().max().item() <= bound, 'call %d' % call
+        assert (got.float() - ref).abs().max().item() <= bound, 'call %d' % call
+
+
+def test_colsum_noalloc_rejects_oversize(cuda_device):
+    from distributed_dot_product import _native
+    lib = _native.load()
+    lib.ddp_colsum_noalloc.argtypes = [ctypes.POINTER(_native.Tensor), ctypes.c_void_p, ctypes.c_void_p]
+    x = torch.zeros(4, 16384 + 8, device=cuda_device)
+    out = torch.zeros(16384 + 8, device=cuda_device)
+    v = _view(_native, x)
+    code = lib.ddp_colsum_noalloc(ctypes.byref(v), ctypes.c_void_p(out.data_ptr()),
+                                  ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+    assert code == -5
+    assert b'16384' in lib.ddp_last_error()
