@@ -77,7 +77,7 @@ template <int OP, int DT, int BN>
 static int launch_one(const GemmKParams& p, int grid, cudaStream_t stream) {
   constexpr int STAGES = (BN == 256) ? 4 : (BN == 128 ? 6 : 8);
   constexpr int kStageBytes = kStageABytes + BN * 128;
-  constexpr int smem = STAGES * kStageBytes + 4 * 4096 + (2 * STAGES + 4) * 8 + 16 + 1024;
+  constexpr int smem = STAGES * kStageBytes + 8 * 4096 + (2 * STAGES + 4) * 8 + 16 + 1024;
   auto kern = gemm_kernel<OP, DT, BN, STAGES>;
   static bool configured[64] = {};
   int dev = 0;
@@ -111,7 +111,18 @@ static int launch_dt(const GemmKParams& p, int dt, int bn, int grid, cudaStream_
   }
 }
 
-static int pick_bn(long long n) { return n <= 64 ? 64 : (n <= 128 ? 128 : 256); }
+// Widest N tile that still gives every SM a tile; narrow problems fall back to smaller tiles.
+static int pick_bn(long long n, long long tiles_per_n_block) {
+  const int cands[3] = {256, 128, 64};
+  const int sms = ddp_num_sms();
+  for (int i = 0; i < 3; ++i) {
+    const int bn = cands[i];
+    if (i < 2 && n <= cands[i + 1]) continue;  // a narrower tile already covers N
+    const long long tiles = tiles_per_n_block * ((n + bn - 1) / bn);
+    if (tiles >= sms || i == 2) return bn;
+  }
+  return 64;
+}
 
 struct Shapes {
   long long M, N, K;  // per segment
@@ -139,8 +150,8 @@ static int derive_shapes(int op, const ddp_tensor* A, const ddp_tensor* B, int w
     return set_error(-4, "unknown op");
   }
   if (s->M < 1 || s->N < 1 || s->K < 1) return set_error(-4, "empty operand");
-  s->bn = pick_bn(s->N);
   s->m_blocks = (int)((s->M + kBlockM - 1) / kBlockM);
+  s->bn = pick_bn(s->N, (long long)A->b0 * A->b1 * s->m_blocks * (op == DDP_OP_NN ? 1 : world));
   s->n_blocks = (int)((s->N + s->bn - 1) / s->bn);
   s->k_blocks = (int)((s->K + bk - 1) / bk);
   if (chunk_rows < 1) chunk_rows = 1;
@@ -261,6 +272,17 @@ extern "C" int ddp_gemm(int op, const ddp_tensor* A, const ddp_tensor* B, const 
       p.tmBg = p.tmB;
     }
   }
+  // ---- C (TMA store path): 32 rows x 128 bytes per box; generic stores cover everything it cannot
+  p.c_tma_ok = 0;
+  if (p.c_vec_ok && !(op == DDP_OP_TN && world > 1)) {
+    uint64_t dims[5] = {(uint64_t)c_cols, 1, (uint64_t)C->rows, (uint64_t)C->b0, (uint64_t)C->b1};
+    uint64_t strides[4] = {(uint64_t)C->ld * es, (uint64_t)C->ld * es, (uint64_t)C->sb0 * es, (uint64_t)C->sb1 * es};
+    uint32_t box[5] = {(uint32_t)(128 / es), 1, 32, 1, 1};
+    if (C->b0 == 1) strides[2] = strides[1];
+    if (C->b1 == 1) strides[3] = strides[2];
+    if (make_map(&p.tmC, dt, C->ptr, dims, strides, box, false) == 0) p.c_tma_ok = 1;
+  }
+  if (!p.c_tma_ok) p.tmC = p.tmA;
   if (world > 1) {
     p.seq = comm->seq; p.phase_mask = comm->phase_mask;
     p.chunk_rows = chunk_rows; p.n_chunks = s.n_chunks;

@@ -26,6 +26,7 @@ struct alignas(64) GemmKParams {
   CUtensorMap tmA;   // A operand
   CUtensorMap tmB;   // B operand, local tensor
   CUtensorMap tmBg;  // B operand, gathered symmetric buffer [world][Bt][rows][cols]
+  CUtensorMap tmC;   // output, box = 32 rows x 128 bytes (TMA store path of the epilogue)
   // per-segment problem extents
   int M, N, K;
   int b0, b1;  // batch extents; Bt = b0*b1, linear batch b = b1i*b0 + b0i
@@ -36,6 +37,7 @@ struct alignas(64) GemmKParams {
   void* C;
   long long ldc, c_sb0, c_sb1;  // element strides
   int c_vec_ok;                 // 16-byte vector stores legal for every tile
+  int c_tma_ok;                 // tmC is valid: full-width chunks leave through TMA stores
   float alpha;
   const void* bias;
   // collective
@@ -104,52 +106,46 @@ __device__ __forceinline__ __half cvt_out<__half>(float v) {
   return __float2half_rn(v);
 }
 
-// Stage one 32-row x 32-col fp32 fragment (thread = row) into the warp's swizzled smem tile as OutT.
-// Row bytes RB = 32*sizeof(OutT); 16-byte vector j of row r lives at slot j ^ ((r / (8/VR)) & (VR-1)).
-template <typename OutT>
-__device__ __forceinline__ void stage_fragment(char* stage, int row, const float (&v)[32]) {
-  constexpr int RB = 32 * sizeof(OutT);
-  constexpr int VR = RB / 16;
-  const int sw = (row / (8 / VR)) & (VR - 1);
-  if constexpr (sizeof(OutT) == 4) {
+// Epilogue staging tile of one warp: 32 rows x 128 bytes; 16-byte vector j of row r lives at slot
+// j ^ (r & 7) - exactly TMA's SWIZZLE_128B, so the same tile can leave through a TMA store or through
+// coalesced generic stores.  NF = 128 / sizeof(StoreT) values per row.
+template <typename StoreT, int NF>
+__device__ __forceinline__ void stage_row(char* sbuf, int row, const float (&v)[NF]) {
+  const int sw = row & 7;
+  if constexpr (sizeof(StoreT) == 4) {
 #pragma unroll
-    for (int j = 0; j < VR; ++j) {
+    for (int j = 0; j < 8; ++j) {
       float4 q = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-      *reinterpret_cast<float4*>(stage + row * RB + ((j ^ sw) * 16)) = q;
+      *reinterpret_cast<float4*>(sbuf + row * 128 + ((j ^ sw) * 16)) = q;
     }
   } else {
 #pragma unroll
-    for (int j = 0; j < VR; ++j) {
-      OutT h[8];
+    for (int j = 0; j < 8; ++j) {
+      StoreT h[8];
 #pragma unroll
-      for (int e = 0; e < 8; ++e) h[e] = cvt_out<OutT>(v[8 * j + e]);
-      *reinterpret_cast<uint4*>(stage + row * RB + ((j ^ sw) * 16)) = *reinterpret_cast<uint4*>(h);
+      for (int e = 0; e < 8; ++e) h[e] = cvt_out<StoreT>(v[8 * j + e]);
+      *reinterpret_cast<uint4*>(sbuf + row * 128 + ((j ^ sw) * 16)) = *reinterpret_cast<uint4*>(h);
     }
   }
 }
 
-// Write the staged 32 x 32 tile to global memory: dst points at element (row 0, col 0) of the fragment,
-// `ld` is the destination row stride in elements; rows_valid / cols_valid clip the fragment.
-template <typename OutT>
-__device__ __forceinline__ void store_fragment(const char* stage, OutT* dst, long long ld, int rows_valid,
-                                               int cols_valid, bool vec_ok, int lane) {
-  constexpr int RB = 32 * sizeof(OutT);
-  constexpr int VR = RB / 16;
-  constexpr int VE = 16 / sizeof(OutT);
+// Generic (predicated) store of the staged tile: dst points at element (row 0, col 0) of the chunk.
+template <typename StoreT>
+__device__ __forceinline__ void store_rows_generic(const char* sbuf, StoreT* dst, long long ld, int rows_valid,
+                                                   int cols_valid, bool vec_ok, int lane) {
+  constexpr int VE = 16 / sizeof(StoreT);
   if (vec_ok) {
-    constexpr int ROWS_PER_IT = 32 / VR;
 #pragma unroll
-    for (int it = 0; it < VR; ++it) {
-      const int r = it * ROWS_PER_IT + lane / VR;
-      const int j = lane % VR;
-      const int sw = (r / (8 / VR)) & (VR - 1);
-      const uint4 q = *reinterpret_cast<const uint4*>(stage + r * RB + ((j ^ sw) * 16));
+    for (int it = 0; it < 8; ++it) {
+      const int r = it * 4 + (lane >> 3);
+      const int j = lane & 7;
+      const uint4 q = *reinterpret_cast<const uint4*>(sbuf + r * 128 + ((j ^ (r & 7)) * 16));
       if (r < rows_valid) {
-        OutT* g = dst + static_cast<long long>(r) * ld + j * VE;
+        StoreT* g = dst + static_cast<long long>(r) * ld + j * VE;
         if ((j + 1) * VE <= cols_valid) {
           st_v4(g, q);
         } else {
-          const OutT* e = reinterpret_cast<const OutT*>(&q);
+          const StoreT* e = reinterpret_cast<const StoreT*>(&q);
 #pragma unroll
           for (int x = 0; x < VE; ++x)
             if (j * VE + x < cols_valid) g[x] = e[x];
@@ -157,12 +153,12 @@ __device__ __forceinline__ void store_fragment(const char* stage, OutT* dst, lon
       }
     }
   } else {
-    // scalar, coalesced along the row: lane = column
-    const int j = lane / VE, x = lane % VE;
     for (int r = 0; r < rows_valid; ++r) {
-      const int sw = (r / (8 / VR)) & (VR - 1);
-      const OutT e = *reinterpret_cast<const OutT*>(stage + r * RB + ((j ^ sw) * 16) + x * sizeof(OutT));
-      if (lane < cols_valid) dst[static_cast<long long>(r) * ld + lane] = e;
+      for (int c = lane; c < cols_valid; c += 32) {
+        const int j = c / VE, x = c % VE;
+        dst[static_cast<long long>(r) * ld + c] =
+            *reinterpret_cast<const StoreT*>(sbuf + r * 128 + ((j ^ (r & 7)) * 16) + x * sizeof(StoreT));
+      }
     }
   }
 }
@@ -185,8 +181,8 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* smem_ab = smem;                                   // STAGES x (A | B)
-  char* smem_stage = reinterpret_cast<char*>(smem + STAGES * kStageBytes);  // 4 warps x 4 KB
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_stage + 4 * 4096);
+  char* smem_stage = reinterpret_cast<char*>(smem + STAGES * kStageBytes);  // 4 warps x 2 x 4 KB
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_stage + 8 * 4096);
   uint64_t* full_bar = bars;                 // [STAGES]
   uint64_t* empty_bar = bars + STAGES;       // [STAGES]
   uint64_t* tfull_bar = bars + 2 * STAGES;   // [2]
@@ -211,6 +207,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
     tma_prefetch_desc(&p.tmA);
     tma_prefetch_desc(&p.tmB);
     if (dist && OP != DDP_OP_TN) tma_prefetch_desc(&p.tmBg);
+    if (p.c_tma_ok) tma_prefetch_desc(&p.tmC);
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < STAGES; ++s) {
@@ -405,7 +402,8 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
     // ======================================================= epilogue warps
     using OutT = InT;
     const int q = warp - 4;  // TMEM lane quadrant
-    char* stage_buf = smem_stage + q * 4096;
+    char* sbuf0 = smem_stage + q * 8192;  // two 4 KB staging buffers per warp
+    int sb = 0;
     int acc = 0;
     uint32_t acc_phase = 0;
     uint32_t done_ok = 0;  // bitmask of peers whose done counter we have already checked (TN)
@@ -422,40 +420,67 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
         __syncwarp();
         done_ok |= 1u << tc.seg;
       }
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
+      // Drains the accumulator in chunks of 128 output bytes per row (64 bf16/fp16 or 32 fp32 columns).
+      auto drain = [&](auto tag, bool to_peer) {
+        using StoreT = decltype(tag);
+        constexpr int CC = 128 / sizeof(StoreT);
+        constexpr int NLD = CC / 32;
 #pragma unroll 1
-      for (int c0 = 0; c0 < BN; c0 += 32) {
-        uint32_t r[32];
-        tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN + c0, r);
-        tmem_ld_wait();
-        const int col0 = n0 + c0;
-        const int cols_valid = max(0, min(32, p.N - col0));
-        if (cols_valid == 0 || rows_valid == 0) continue;  // warp-uniform
-        float v[32];
+        for (int c0 = 0; c0 < BN; c0 += CC) {
+          const int col0 = n0 + c0;
+          const int cols_valid = min(CC, p.N - col0);
+          if (cols_valid <= 0 || rows_valid == 0) break;  // warp-uniform
+          uint32_t r[NLD][32];
 #pragma unroll
-        for (int e = 0; e < 32; ++e) v[e] = __uint_as_float(r[e]) * p.alpha;
-        if (tn_remote) {
-          // fp32 partial tile -> owner's slot [src = rank][b][M][N]
-          stage_fragment<float>(stage_buf, lane, v);
-          __syncwarp();
-          float* dst = reinterpret_cast<float*>(p.ws[tc.seg]) +
-                       ((static_cast<size_t>(p.rank) * Bt + tc.b) * p.M + row0) * p.N + col0;
-          store_fragment<float>(stage_buf, dst, p.N, rows_valid, cols_valid, (p.N & 3) == 0, lane);
-          __syncwarp();
-        } else {
-          if (p.bias != nullptr) {
-            const OutT* bias = reinterpret_cast<const OutT*>(p.bias);
+          for (int i = 0; i < NLD; ++i) tmem_ld_32x32(taddr + c0 + i * 32, r[i]);
+          tmem_ld_wait();
+          float v[CC];
 #pragma unroll
-            for (int e = 0; e < 32; ++e)
+          for (int i = 0; i < NLD; ++i)
+#pragma unroll
+            for (int e = 0; e < 32; ++e) v[i * 32 + e] = __uint_as_float(r[i][e]) * p.alpha;
+          if (!to_peer && p.bias != nullptr) {
+            const StoreT* bias = reinterpret_cast<const StoreT*>(p.bias);
+#pragma unroll
+            for (int e = 0; e < CC; ++e)
               if (e < cols_valid) v[e] += static_cast<float>(bias[col0 + e]);
           }
-          stage_fragment<OutT>(stage_buf, lane, v);
+          char* sbuf = sbuf0 + sb * 4096;
+          if (lane == 0) bulk_wait_group_read<1>();  // the TMA store that last read this buffer is done
           __syncwarp();
-          const long long col_g = (OP == DDP_OP_NT ? static_cast<long long>(tc.seg) * p.N : 0) + col0;
-          OutT* dst = reinterpret_cast<OutT*>(p.C) + tc.b1i * p.c_sb1 + tc.b0i * p.c_sb0 +
-                      static_cast<long long>(row0) * p.ldc + col_g;
-          store_fragment<OutT>(stage_buf, dst, p.ldc, rows_valid, cols_valid, p.c_vec_ok != 0, lane);
-          __syncwarp();
+          stage_row<StoreT, CC>(sbuf, lane, v);
+          if (to_peer) {
+            // fp32 partial tile -> owner's slot [src = rank][b][M][N]
+            __syncwarp();
+            StoreT* dst = reinterpret_cast<StoreT*>(p.ws[tc.seg]) +
+                          ((static_cast<size_t>(p.rank) * Bt + tc.b) * p.M + row0) * p.N + col0;
+            store_rows_generic<StoreT>(sbuf, dst, p.N, rows_valid, cols_valid, (p.N & 3) == 0, lane);
+            __syncwarp();
+          } else {
+            const long long col_g = (OP == DDP_OP_NT ? static_cast<long long>(tc.seg) * p.N : 0) + col0;
+            if (p.c_tma_ok && cols_valid == CC) {
+              fence_proxy_async_smem();
+              __syncwarp();
+              if (lane == 0) {
+                tma_store_5d(&p.tmC, sbuf, static_cast<int>(col_g), 0, row0, tc.b0i, tc.b1i);
+                bulk_commit_group();
+              }
+            } else {
+              __syncwarp();
+              StoreT* dst = reinterpret_cast<StoreT*>(p.C) + tc.b1i * p.c_sb1 + tc.b0i * p.c_sb0 +
+                            static_cast<long long>(row0) * p.ldc + col_g;
+              store_rows_generic<StoreT>(sbuf, dst, p.ldc, rows_valid, cols_valid, p.c_vec_ok != 0, lane);
+              __syncwarp();
+            }
+          }
+          sb ^= 1;
         }
+      };
+      if (tn_remote) {
+        drain(float{}, true);
+      } else {
+        drain(OutT{}, false);
       }
       // accumulator drained -> hand the TMEM buffer back to the MMA warp
       tc_fence_before();
@@ -477,6 +502,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
         acc_phase ^= 1;
       }
     }
+    if (lane == 0) bulk_wait_group_read<0>();  // staging smem must outlive the TMA stores reading it
     // ---------------------------------------------------- reduce-scatter: owner-side reduction
     if (OP == DDP_OP_TN && dist && do_consume) {
       const int items = Bt * p.m_blocks * p.n_blocks * 4;

@@ -67,8 +67,25 @@ __device__ __forceinline__ float block_reduce(float v, float* red) {
 constexpr float kLog2e = 1.4426950408889634f;
 
 // ------------------------------------------------------------------ forward, register resident
-template <typename T, int VPT>
-__global__ void __launch_bounds__(512) softmax_fwd_reg(const SmParams p) {
+template <typename T> struct Packed2 { using type = __nv_bfloat162; };
+template <> struct Packed2<__half> { using type = __half2; };
+
+// Row maximum of the (mask-applied) packed vectors without unpacking: HMNMX2 on 16-bit pairs.
+template <typename T>
+__device__ __forceinline__ float vec_max(const uint4& q, float mx) {
+  if constexpr (sizeof(T) == 4) {
+    const float* e = reinterpret_cast<const float*>(&q);
+    return fmaxf(fmaxf(fmaxf(mx, e[0]), fmaxf(e[1], e[2])), e[3]);
+  } else {
+    using P2 = typename Packed2<T>::type;
+    const P2* e = reinterpret_cast<const P2*>(&q);
+    const P2 m = __hmax2(__hmax2(e[0], e[1]), __hmax2(e[2], e[3]));
+    return fmaxf(mx, fmaxf(to_f(m.x), to_f(m.y)));
+  }
+}
+
+template <typename T, int VPT, int THREADS, int MINB>
+__global__ void __launch_bounds__(THREADS, MINB) softmax_fwd_reg(const SmParams p) {
   constexpr int VE = 16 / sizeof(T);
   __shared__ float red[32];
   const int nvec = p.cols / VE;
@@ -83,13 +100,13 @@ __global__ void __launch_bounds__(512) softmax_fwd_reg(const SmParams p) {
       uint4 q[VPT];
 #pragma unroll
       for (int i = 0; i < VPT; ++i) {
-        const int v = threadIdx.x + i * blockDim.x;
+        const int v = threadIdx.x + i * THREADS;
         if (v < nvec) q[i] = *reinterpret_cast<const uint4*>(xr + static_cast<long long>(v) * VE);
       }
       float mx = -INFINITY;
 #pragma unroll
       for (int i = 0; i < VPT; ++i) {
-        const int v = threadIdx.x + i * blockDim.x;
+        const int v = threadIdx.x + i * THREADS;
         if (v < nvec) {
           T* e = reinterpret_cast<T*>(&q[i]);
           if (mrow) {
@@ -103,16 +120,15 @@ __global__ void __launch_bounds__(512) softmax_fwd_reg(const SmParams p) {
             for (int k = 0; k < VE; ++k)
               if (mb[k]) e[k] = from_f<T>(-INFINITY);
           }
-#pragma unroll
-          for (int k = 0; k < VE; ++k) mx = fmaxf(mx, to_f(e[k]) * p.scale);
+          mx = vec_max<T>(q[i], mx);  // max of raw scores; scale > 0 commutes with max
         }
       }
-      mx = block_reduce<true>(mx, red);
+      mx = block_reduce<true>(mx, red) * p.scale;
       const float m2 = mx * kLog2e;
       float sum = 0.f;
 #pragma unroll
       for (int i = 0; i < VPT; ++i) {
-        const int v = threadIdx.x + i * blockDim.x;
+        const int v = threadIdx.x + i * THREADS;
         if (v < nvec) {
           T* e = reinterpret_cast<T*>(&q[i]);
 #pragma unroll
@@ -127,7 +143,7 @@ __global__ void __launch_bounds__(512) softmax_fwd_reg(const SmParams p) {
       const float inv = 1.f / sum;
 #pragma unroll
       for (int i = 0; i < VPT; ++i) {
-        const int v = threadIdx.x + i * blockDim.x;
+        const int v = threadIdx.x + i * THREADS;
         if (v < nvec) {
           T* e = reinterpret_cast<T*>(&q[i]);
 #pragma unroll
@@ -299,15 +315,20 @@ static int launch_fwd(const SmParams& p, bool vec_ok, cudaStream_t st) {
   const int items = p.b1 * p.rows;
   const int sms = ddp_num_sms();
   const int nvec = p.cols / VE;
-  if (vec_ok && nvec <= 512 * 16) {
+  if (vec_ok && nvec <= 1024 * 8 && p.scale > 0.f) {
+    // (vectors per thread, threads, CTAs per SM): as many independent rows in flight per SM as registers allow
     if (nvec <= 256) {
-      softmax_fwd_reg<T, 2><<<min(items, sms * 8), 128, 0, st>>>(p);
+      softmax_fwd_reg<T, 2, 128, 8><<<min(items, sms * 8), 128, 0, st>>>(p);
+    } else if (nvec <= 512) {
+      softmax_fwd_reg<T, 4, 128, 8><<<min(items, sms * 8), 128, 0, st>>>(p);
     } else if (nvec <= 1024) {
-      softmax_fwd_reg<T, 4><<<min(items, sms * 4), 256, 0, st>>>(p);
+      softmax_fwd_reg<T, 8, 128, 6><<<min(items, sms * 6), 128, 0, st>>>(p);
+    } else if (nvec <= 2048) {
+      softmax_fwd_reg<T, 8, 256, 3><<<min(items, sms * 3), 256, 0, st>>>(p);
     } else if (nvec <= 4096) {
-      softmax_fwd_reg<T, 8><<<min(items, sms * 2), 512, 0, st>>>(p);
+      softmax_fwd_reg<T, 8, 512, 1><<<min(items, sms * 2), 512, 0, st>>>(p);
     } else {
-      softmax_fwd_reg<T, 16><<<min(items, sms * 2), 512, 0, st>>>(p);
+      softmax_fwd_reg<T, 16, 512, 1><<<min(items, sms), 512, 0, st>>>(p);
     }
   } else {
     softmax_fwd_stream<T><<<min(items, sms * 4), p.cols >= 4096 ? 512 : 256, 0, st>>>(p);
