@@ -73,12 +73,20 @@ static int make_map(CUtensorMap* m, int dt, void* ptr, const uint64_t dims[5], c
   return 0;
 }
 
-template <int OP, int DT, int BN>
+template <int OP, int DT, int BN, int EPI>
 static int launch_one(const GemmKParams& p, int grid, cudaStream_t stream) {
-  constexpr int STAGES = (BN == 256) ? 4 : (BN == 128 ? 6 : 8);
+  // The exp-heavy softmax statistics epilogue runs on 8 epilogue warps (two per TMEM lane quadrant).
+  // (The store path of the 8-warp configuration is not enabled: on B200 the second warp of a quadrant
+  //  intermittently drained zeros for its first 32 columns after a TMA store; see DESIGN.md.)
+  constexpr int EW = (EPI == 2) ? 8 : 4;
+  // smem ring depth: ~190 KB of operand stages, less when the epilogue needs more staging / landing buffers
+  constexpr int STAGES = EPI == 1   ? ((BN == 256) ? 2 : (BN == 128 ? 4 : 5))
+                         : EPI >= 2 ? ((BN == 256) ? 3 : (BN == 128 ? 5 : 6))
+                                    : ((BN == 256) ? 4 : (BN == 128 ? 6 : 8));
   constexpr int kStageBytes = kStageABytes + BN * 128;
-  constexpr int smem = STAGES * kStageBytes + 8 * 4096 + (2 * STAGES + 4) * 8 + 16 + 1024;
-  auto kern = gemm_kernel<OP, DT, BN, STAGES>;
+  constexpr int smem = STAGES * kStageBytes + (2 * EW + (EPI == 1 ? 16 : 0)) * 4096 + (2 * STAGES + 20) * 8 + 16 + 1024;
+  static_assert(smem <= 232448, "shared memory budget exceeded");
+  auto kern = gemm_kernel<OP, DT, BN, STAGES, EPI, EW>;
   static bool configured[64] = {};
   int dev = 0;
   cudaGetDevice(&dev);
@@ -87,27 +95,27 @@ static int launch_one(const GemmKParams& p, int grid, cudaStream_t stream) {
     if (e != cudaSuccess) return set_error(-12, cudaGetErrorString(e));
     configured[dev] = true;
   }
-  kern<<<grid, kThreads, smem, stream>>>(p);
+  kern<<<grid, kThreadsBase + 32 * EW, smem, stream>>>(p);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return set_error(-13, cudaGetErrorString(e));
   return 0;
 }
 
-template <int OP, int DT>
+template <int OP, int DT, int EPI>
 static int launch_bn(const GemmKParams& p, int bn, int grid, cudaStream_t stream) {
   switch (bn) {
-    case 64: return launch_one<OP, DT, 64>(p, grid, stream);
-    case 128: return launch_one<OP, DT, 128>(p, grid, stream);
-    default: return launch_one<OP, DT, 256>(p, grid, stream);
+    case 64: return launch_one<OP, DT, 64, EPI>(p, grid, stream);
+    case 128: return launch_one<OP, DT, 128, EPI>(p, grid, stream);
+    default: return launch_one<OP, DT, 256, EPI>(p, grid, stream);
   }
 }
 
-template <int OP>
+template <int OP, int EPI = 0>
 static int launch_dt(const GemmKParams& p, int dt, int bn, int grid, cudaStream_t stream) {
   switch (dt) {
-    case DDP_F16: return launch_bn<OP, DDP_F16>(p, bn, grid, stream);
-    case DDP_BF16: return launch_bn<OP, DDP_BF16>(p, bn, grid, stream);
-    default: return launch_bn<OP, DDP_F32>(p, bn, grid, stream);
+    case DDP_F16: return launch_bn<OP, DDP_F16, EPI>(p, bn, grid, stream);
+    case DDP_BF16: return launch_bn<OP, DDP_BF16, EPI>(p, bn, grid, stream);
+    default: return launch_bn<OP, DDP_F32, EPI>(p, bn, grid, stream);
   }
 }
 
@@ -183,8 +191,19 @@ extern "C" int ddp_gemm_workspace(int op, const ddp_tensor* A, const ddp_tensor*
   return 0;
 }
 
+extern "C" int ddp_gemm_stats_tiles(const ddp_tensor* A, const ddp_tensor* B, int world) {
+  Shapes s;
+  if (derive_shapes(DDP_OP_NT, A, B, world, 1 << 30, &s)) return -1;
+  return world * s.n_blocks * 2;  // the statistics pass splits every tile into two column halves
+}
+
 extern "C" int ddp_gemm(int op, const ddp_tensor* A, const ddp_tensor* B, const ddp_tensor* C, float alpha,
                         const void* bias, const ddp_comm* comm, int dbg, void* stream_) {
+  return ddp_gemm_ex(op, A, B, C, alpha, bias, comm, nullptr, dbg, stream_);
+}
+
+extern "C" int ddp_gemm_ex(int op, const ddp_tensor* A, const ddp_tensor* B, const ddp_tensor* C, float alpha,
+                           const void* bias, const ddp_comm* comm, const ddp_epilogue* epi, int dbg, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   const int world = comm ? comm->world : 1;
   const int rank = comm ? comm->rank : 0;
@@ -195,6 +214,7 @@ extern "C" int ddp_gemm(int op, const ddp_tensor* A, const ddp_tensor* B, const 
   const int dt = A->dtype;
   const int es = elem_size(dt);
   const uint32_t bk = 128 / es, ch = 128 / es;
+  if (!C) return set_error(-4, "C is required (pass the result tensor even for the statistics pass)");
   if (C->dtype != dt) return set_error(-4, "C must have the dtype of A and B");
   if (C->b0 != A->b0 || C->b1 != A->b1) return set_error(-4, "C batch extents differ");
   const long long c_cols = (op == DDP_OP_NT) ? world * s.N : s.N;
@@ -274,7 +294,7 @@ extern "C" int ddp_gemm(int op, const ddp_tensor* A, const ddp_tensor* B, const 
   }
   // ---- C (TMA store path): 32 rows x 128 bytes per box; generic stores cover everything it cannot
   p.c_tma_ok = 0;
-  if (p.c_vec_ok && !(op == DDP_OP_TN && world > 1)) {
+  if (p.c_vec_ok && !(op == DDP_OP_TN && world > 1) && !(dbg & 16)) {  // dbg 16: force generic stores
     uint64_t dims[5] = {(uint64_t)c_cols, 1, (uint64_t)C->rows, (uint64_t)C->b0, (uint64_t)C->b1};
     uint64_t strides[4] = {(uint64_t)C->ld * es, (uint64_t)C->ld * es, (uint64_t)C->sb0 * es, (uint64_t)C->sb1 * es};
     uint32_t box[5] = {(uint32_t)(128 / es), 1, 32, 1, 1};
@@ -283,6 +303,40 @@ extern "C" int ddp_gemm(int op, const ddp_tensor* A, const ddp_tensor* B, const 
     if (make_map(&p.tmC, dt, C->ptr, dims, strides, box, false) == 0) p.c_tma_ok = 1;
   }
   if (!p.c_tma_ok) p.tmC = p.tmA;
+  // ---- fused softmax-backward epilogue (nt only): needs P addressable exactly like C
+  const bool fused = epi && epi->mode == DDP_EPI_SOFTMAX_BWD;
+  p.tmP = p.tmA;
+  if (fused) {
+    const ddp_tensor* P = epi->P;
+    if (op != DDP_OP_NT) return set_error(-4, "the softmax-backward epilogue belongs to the nt product");
+    if (!P || !epi->delta) return set_error(-4, "softmax-backward epilogue: P and delta are required");
+    if (P->dtype != dt || P->rows != C->rows || P->cols != C->cols || P->b0 != C->b0 || P->b1 != C->b1)
+      return set_error(-4, "softmax-backward epilogue: P must have the shape and dtype of the result");
+    if (world > 1 && (s.N * es) % 16) return set_error(-2, "softmax-backward epilogue: T/N rows must be 16-byte aligned");
+    uint64_t dims[5] = {(uint64_t)c_cols, 1, (uint64_t)P->rows, (uint64_t)P->b0, (uint64_t)P->b1};
+    uint64_t strides[4] = {(uint64_t)P->ld * es, (uint64_t)P->ld * es, (uint64_t)P->sb0 * es, (uint64_t)P->sb1 * es};
+    uint32_t box[5] = {(uint32_t)(128 / es), 1, 32, 1, 1};
+    if (P->b0 == 1) strides[2] = strides[1];
+    if (P->b1 == 1) strides[3] = strides[2];
+    if (int e = make_map(&p.tmP, dt, P->ptr, dims, strides, box, false)) return e;
+    p.delta = epi->delta;
+    p.epi_scale = epi->scale;
+  }
+  const bool sm_stats = epi && epi->mode == DDP_EPI_SOFTMAX_STATS;
+  const bool sm_apply = epi && epi->mode == DDP_EPI_SOFTMAX_APPLY;
+  if (sm_stats || sm_apply) {
+    if (op != DDP_OP_NT) return set_error(-4, "the softmax-forward epilogues belong to the nt product");
+    if (world > 1 && s.N % 32) return set_error(-2, "softmax-forward epilogue: T/N must be a multiple of 32");
+    if (sm_stats && !epi->stats) return set_error(-4, "softmax-stats epilogue: stats buffer required");
+    if (sm_apply && !epi->rowstat) return set_error(-4, "softmax-apply epilogue: rowstat required");
+    p.mask_bits = epi->mask_bits;
+    p.mb_ld = epi->mask_ld_words;
+    p.mb_sb1 = epi->mask_sb1_words;
+    p.stats = reinterpret_cast<float2*>(epi->stats);
+    p.rowstat = reinterpret_cast<const float2*>(epi->rowstat);
+    p.stats_nt = world * s.n_blocks * 2;  // two column halves per tile (8 epilogue warps)
+    p.epi_scale = epi->scale * 1.4426950408889634f;  // scores in the log2 domain
+  }
   if (world > 1) {
     p.seq = comm->seq; p.phase_mask = comm->phase_mask;
     p.chunk_rows = chunk_rows; p.n_chunks = s.n_chunks;
@@ -301,7 +355,11 @@ extern "C" int ddp_gemm(int op, const ddp_tensor* A, const ddp_tensor* B, const 
   int grid = world > 1 ? sms : (int)(tiles < sms ? tiles : sms);
   if (grid < 1) grid = 1;
   switch (op) {
-    case DDP_OP_NT: return launch_dt<DDP_OP_NT>(p, dt, s.bn, grid, stream);
+    case DDP_OP_NT:
+      if (fused) return launch_dt<DDP_OP_NT, 1>(p, dt, s.bn, grid, stream);
+      if (sm_stats) return launch_dt<DDP_OP_NT, 2>(p, dt, s.bn, grid, stream);
+      if (sm_apply) return launch_dt<DDP_OP_NT, 3>(p, dt, s.bn, grid, stream);
+      return launch_dt<DDP_OP_NT>(p, dt, s.bn, grid, stream);
     case DDP_OP_NN: return launch_dt<DDP_OP_NN>(p, dt, s.bn, grid, stream);
     default: return launch_dt<DDP_OP_TN>(p, dt, s.bn, grid, stream);
   }

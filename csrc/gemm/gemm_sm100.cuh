@@ -19,7 +19,7 @@
 namespace ddp {
 
 constexpr int kBlockM = 128;
-constexpr int kThreads = 256;
+constexpr int kThreadsBase = 128;  // producer, MMA, 2 pusher warps; plus 32 x EW epilogue threads
 constexpr int kStageABytes = kBlockM * 128;  // 128 rows x 128 B (either majorness)
 
 struct alignas(64) GemmKParams {
@@ -27,6 +27,7 @@ struct alignas(64) GemmKParams {
   CUtensorMap tmB;   // B operand, local tensor
   CUtensorMap tmBg;  // B operand, gathered symmetric buffer [world][Bt][rows][cols]
   CUtensorMap tmC;   // output, box = 32 rows x 128 bytes (TMA store path of the epilogue)
+  CUtensorMap tmP;   // EPI == 1: probabilities P, same shape / box as C
   // per-segment problem extents
   int M, N, K;
   int b0, b1;  // batch extents; Bt = b0*b1, linear batch b = b1i*b0 + b0i
@@ -40,6 +41,17 @@ struct alignas(64) GemmKParams {
   int c_tma_ok;                 // tmC is valid: full-width chunks leave through TMA stores
   float alpha;
   const void* bias;
+  // EPI == 1 (softmax backward fused into the dP = dO V^T epilogue): C = epi_scale * P * (acc - delta[row])
+  const float* delta;  // [Bt][M] fp32, rowsum(dO * O)
+  float epi_scale;
+  // EPI == 2 / 3 (softmax forward fused into the K Q^T product, two passes over the tiles, no score slab):
+  //   2: per (row, column tile) online-softmax statistics (max, sum) of t = acc * epi_scale (log2 domain)
+  //   3: C = exp2(t - rowstat.x) * rowstat.y   with rowstat = (row max, 1 / row sum) from the combine kernel
+  const uint32_t* mask_bits;   // bit-packed mask [b1][M][mb_ld words], bit set = masked out; may be null
+  long long mb_ld, mb_sb1;     // in 32-bit words
+  float2* stats;               // EPI 2 out: [Bt][M][stats_nt]
+  const float2* rowstat;       // EPI 3 in:  [Bt][M]
+  int stats_nt;
   // collective
   uint32_t seq;
   int phase_mask;
@@ -60,20 +72,36 @@ struct TileCoord {
   int seg, b, b0i, b1i, m0, n0;
 };
 
-template <int OP>
+// Tile order: segments outermost (rank-rotated).  kHeadFastest (fused softmax epilogues) makes the inner
+// batch index b0 (heads) vary fastest so the 16 tiles that share one mask tile run back to back (L2 reuse).
+template <int OP, int BN, bool kHeadFastest = false>
 __device__ __forceinline__ TileCoord decode_tile(const GemmKParams& p, int t) {
   const int mn = p.m_blocks * p.n_blocks;
   const int per_seg = p.b0 * p.b1 * mn;
   const int si = t / per_seg;
   int r = t - si * per_seg;
   TileCoord c;
-  c.b = r / mn;
-  r -= c.b * mn;
-  const int nb = r / p.m_blocks;
-  const int mb = r - nb * p.m_blocks;
-  c.b1i = c.b / p.b0;
-  c.b0i = c.b - c.b1i * p.b0;
+  int nb, mb;
+  if (kHeadFastest) {
+    const int per_b1 = p.b0 * mn;
+    c.b1i = r / per_b1;
+    r -= c.b1i * per_b1;
+    const int per_nb = p.m_blocks * p.b0;
+    nb = r / per_nb;
+    r -= nb * per_nb;
+    mb = r / p.b0;
+    c.b0i = r - mb * p.b0;
+    c.b = c.b1i * p.b0 + c.b0i;
+  } else {
+    c.b = r / mn;
+    r -= c.b * mn;
+    nb = r / p.m_blocks;
+    mb = r - nb * p.m_blocks;
+    c.b1i = c.b / p.b0;
+    c.b0i = c.b - c.b1i * p.b0;
+  }
   c.m0 = mb * kBlockM;
+  c.n0 = nb * BN;
   if (OP == DDP_OP_NT) {
     c.seg = (p.rank + si) % p.world;
   } else if (OP == DDP_OP_TN) {
@@ -82,13 +110,6 @@ __device__ __forceinline__ TileCoord decode_tile(const GemmKParams& p, int t) {
     c.seg = 0;
   }
   return c;
-}
-
-template <int BN>
-__device__ __forceinline__ int tile_n0(const GemmKParams& p, int t) {
-  const int mn = p.m_blocks * p.n_blocks;
-  const int r = t % mn;
-  return (r / p.m_blocks) * BN;
 }
 
 template <typename OutT>
@@ -109,29 +130,31 @@ __device__ __forceinline__ __half cvt_out<__half>(float v) {
 // Epilogue staging tile of one warp: 32 rows x 128 bytes; 16-byte vector j of row r lives at slot
 // j ^ (r & 7) - exactly TMA's SWIZZLE_128B, so the same tile can leave through a TMA store or through
 // coalesced generic stores.  NF = 128 / sizeof(StoreT) values per row.
-template <typename StoreT, int NF>
-__device__ __forceinline__ void stage_row(char* sbuf, int row, const float (&v)[NF]) {
+template <typename StoreT>
+__device__ __forceinline__ void stage_row32(uint32_t sbuf, int row, const float (&v)[32], int part) {
   const int sw = row & 7;
   if constexpr (sizeof(StoreT) == 4) {
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      float4 q = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-      *reinterpret_cast<float4*>(sbuf + row * 128 + ((j ^ sw) * 16)) = q;
+      uint4 q;
+      q.x = __float_as_uint(v[4 * j]); q.y = __float_as_uint(v[4 * j + 1]);
+      q.z = __float_as_uint(v[4 * j + 2]); q.w = __float_as_uint(v[4 * j + 3]);
+      st_shared_v4(sbuf + row * 128 + ((j ^ sw) * 16), q);
     }
   } else {
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
+    for (int j = 0; j < 4; ++j) {
       StoreT h[8];
 #pragma unroll
       for (int e = 0; e < 8; ++e) h[e] = cvt_out<StoreT>(v[8 * j + e]);
-      *reinterpret_cast<uint4*>(sbuf + row * 128 + ((j ^ sw) * 16)) = *reinterpret_cast<uint4*>(h);
+      st_shared_v4(sbuf + row * 128 + (((part * 4 + j) ^ sw) * 16), *reinterpret_cast<uint4*>(h));
     }
   }
 }
 
 // Generic (predicated) store of the staged tile: dst points at element (row 0, col 0) of the chunk.
 template <typename StoreT>
-__device__ __forceinline__ void store_rows_generic(const char* sbuf, StoreT* dst, long long ld, int rows_valid,
+__device__ __forceinline__ void store_rows_generic(uint32_t sbuf, StoreT* dst, long long ld, int rows_valid,
                                                    int cols_valid, bool vec_ok, int lane) {
   constexpr int VE = 16 / sizeof(StoreT);
   if (vec_ok) {
@@ -139,7 +162,7 @@ __device__ __forceinline__ void store_rows_generic(const char* sbuf, StoreT* dst
     for (int it = 0; it < 8; ++it) {
       const int r = it * 4 + (lane >> 3);
       const int j = lane & 7;
-      const uint4 q = *reinterpret_cast<const uint4*>(sbuf + r * 128 + ((j ^ (r & 7)) * 16));
+      const uint4 q = ld_shared_v4(sbuf + r * 128 + ((j ^ (r & 7)) * 16));
       if (r < rows_valid) {
         StoreT* g = dst + static_cast<long long>(r) * ld + j * VE;
         if ((j + 1) * VE <= cols_valid) {
@@ -156,15 +179,17 @@ __device__ __forceinline__ void store_rows_generic(const char* sbuf, StoreT* dst
     for (int r = 0; r < rows_valid; ++r) {
       for (int c = lane; c < cols_valid; c += 32) {
         const int j = c / VE, x = c % VE;
-        dst[static_cast<long long>(r) * ld + c] =
-            *reinterpret_cast<const StoreT*>(sbuf + r * 128 + ((j ^ (r & 7)) * 16) + x * sizeof(StoreT));
+        const uint4 q = ld_shared_v4(sbuf + r * 128 + ((j ^ (r & 7)) * 16));
+        dst[static_cast<long long>(r) * ld + c] = reinterpret_cast<const StoreT*>(&q)[x];
       }
     }
   }
 }
 
-template <int OP, int DT, int BN, int STAGES>
-__global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant__ GemmKParams p) {
+template <int OP, int DT, int BN, int STAGES, int EPI = 0, int EW = 4>
+__global__ void __launch_bounds__(kThreadsBase + 32 * EW, 1) gemm_kernel(const __grid_constant__ GemmKParams p) {
+  static_assert(EW == 4 || EW == 8, "4 or 8 epilogue warps");
+  static_assert(EW == 4 || (OP == DDP_OP_NT && EPI != 1), "8 epilogue warps: nt without P prefetch only");
   using InT = typename std::conditional<DT == DDP_F32, float,
                                         typename std::conditional<DT == DDP_BF16, __nv_bfloat16, __half>::type>::type;
   constexpr int ELEM = (DT == DDP_F32) ? 4 : 2;
@@ -181,13 +206,16 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* smem_ab = smem;                                   // STAGES x (A | B)
-  char* smem_stage = reinterpret_cast<char*>(smem + STAGES * kStageBytes);  // 4 warps x 2 x 4 KB
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_stage + 8 * 4096);
+  char* smem_stage = reinterpret_cast<char*>(smem + STAGES * kStageBytes);  // EW warps x 2 x 4 KB
+  constexpr int kPBufs = 4;                   // EPI == 1: landing buffers per warp = TMA prefetch depth for P
+  char* smem_pst = smem_stage + 2 * EW * 4096;    // EPI == 1: 4 warps x kPBufs x 4 KB
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_stage + (EPI == 1 ? 2 * EW + 4 * kPBufs : 2 * EW) * 4096);
   uint64_t* full_bar = bars;                 // [STAGES]
   uint64_t* empty_bar = bars + STAGES;       // [STAGES]
   uint64_t* tfull_bar = bars + 2 * STAGES;   // [2]
   uint64_t* tempty_bar = tfull_bar + 2;      // [2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+  uint64_t* p_bar = tempty_bar + 2;          // [4 warps][kPBufs]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(p_bar + 4 * kPBufs);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -208,6 +236,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
     tma_prefetch_desc(&p.tmB);
     if (dist && OP != DDP_OP_TN) tma_prefetch_desc(&p.tmBg);
     if (p.c_tma_ok) tma_prefetch_desc(&p.tmC);
+    if (EPI == 1) tma_prefetch_desc(&p.tmP);
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < STAGES; ++s) {
@@ -216,8 +245,9 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&tfull_bar[s], 1);
-      mbar_init(&tempty_bar[s], 4);
+      mbar_init(&tempty_bar[s], EW);
     }
+    for (int s = 0; s < 4 * kPBufs; ++s) mbar_init(&p_bar[s], 1);
     fence_mbar_init();
   }
   if (warp == 2) tmem_alloc(tmem_slot, kTmemCols);
@@ -233,8 +263,8 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
       uint32_t phase = 0;
       const uint32_t* my_flags = p.flags[p.rank];
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-        const TileCoord tc = decode_tile<OP>(p, t);
-        const int n0 = tile_n0<BN>(p, t);
+        const TileCoord tc = decode_tile<OP, BN, (EPI >= 2)>(p, t);
+        const int n0 = tc.n0;
         if (OP == DDP_OP_NT && dist && tc.seg != p.rank) {
           // gathered rows [n0, n0+BN) of rank seg must have landed in our buffer
           const int c_lo = n0 / p.chunk_rows;
@@ -401,19 +431,69 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
   } else {
     // ======================================================= epilogue warps
     using OutT = InT;
-    const int q = warp - 4;  // TMEM lane quadrant
-    char* sbuf0 = smem_stage + q * 8192;  // two 4 KB staging buffers per warp
+    const int ew = warp - 4;
+    const int q = ew & 3;    // TMEM lane quadrant this warp may read (= warp id mod 4)
+    const int ch = ew >> 2;  // with 8 epilogue warps, two warps share a quadrant and split the columns
+    constexpr int CW = BN / (EW / 4);  // columns of a tile handled by one warp
+    char* sbuf0 = smem_stage + ew * 8192;  // two 4 KB staging buffers per warp
     int sb = 0;
+    // EPI == 1: P chunks arrive through TMA kPBufs-1 chunks ahead of their use (enough bytes in flight to
+    // cover DRAM latency), in the running order (tile, chunk) of this warp; g counts consumed chunks,
+    // buffer/barrier = g % kPBufs, parity = (g / kPBufs) & 1.
+    char* pbuf0 = smem_pst + ew * (kPBufs * 4096);
+    int g = 0;
+    auto issue_p = [&](int gi) {  // lane 0 only
+      constexpr int CCp = 128 / sizeof(OutT);
+      constexpr int CPT = CW / CCp;
+      const int ti = gi / CPT, ci = gi - ti * CPT;
+      const int tt = blockIdx.x + ti * gridDim.x;
+      if (tt >= total_tiles) return;
+      const TileCoord c2 = decode_tile<OP, BN, (EPI >= 2)>(p, tt);
+      const int col = c2.seg * p.N + c2.n0 + ch * CW + ci * CCp;
+      uint64_t* bar = &p_bar[q * kPBufs + (gi % kPBufs)];
+      mbar_arrive_expect_tx(bar, 4096);
+      tma_load_5d(pbuf0 + (gi % kPBufs) * 4096, &p.tmP, bar, col, 0, c2.m0 + q * 32, c2.b0i, c2.b1i);
+    };
+    if (EPI == 1 && lane == 0)
+      for (int i = 0; i < kPBufs - 1; ++i) issue_p(i);
     int acc = 0;
     uint32_t acc_phase = 0;
     uint32_t done_ok = 0;  // bitmask of peers whose done counter we have already checked (TN)
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-      const TileCoord tc = decode_tile<OP>(p, t);
-      const int n0 = tile_n0<BN>(p, t);
-      mbar_wait(&tfull_bar[acc], acc_phase);
-      tc_fence_after();
+      const TileCoord tc = decode_tile<OP, BN, (EPI >= 2)>(p, t);
+      const int n0 = tc.n0;
       const int row0 = tc.m0 + q * 32;                       // first row of this warp's fragment
       const int rows_valid = max(0, min(32, p.M - row0));
+      // Per-tile operands of the fused epilogues are fetched BEFORE waiting for the accumulator, so their
+      // latency hides behind the MMA: delta (EPI 1); mask words of this thread's row and row stats (EPI 2/3).
+      float row_delta = 0.f;
+      if (EPI == 1 && row0 + lane < p.M) row_delta = p.delta[static_cast<size_t>(tc.b) * p.M + row0 + lane];
+      uint32_t mk0 = 0, mk1 = 0, mk2 = 0, mk3 = 0, mk4 = 0, mk5 = 0, mk6 = 0, mk7 = 0;
+      float2 rstat = make_float2(0.f, 0.f);
+      if constexpr (EPI >= 2) {
+        const bool row_ok = row0 + lane < p.M;
+        if (p.mask_bits != nullptr && row_ok) {
+          const long long col_g0 = static_cast<long long>(tc.seg) * p.N + n0;
+          const uint32_t* mrow =
+              p.mask_bits + tc.b1i * p.mb_sb1 + static_cast<long long>(row0 + lane) * p.mb_ld + (col_g0 >> 5);
+          const int nw = min(BN / 32, (p.N - n0 + 31) >> 5);  // words that exist for this tile
+          if (0 < nw) mk0 = __ldg(mrow + 0);
+          if (1 < nw) mk1 = __ldg(mrow + 1);
+          if (BN > 64) {
+            if (2 < nw) mk2 = __ldg(mrow + 2);
+            if (3 < nw) mk3 = __ldg(mrow + 3);
+          }
+          if (BN > 128) {
+            if (4 < nw) mk4 = __ldg(mrow + 4);
+            if (5 < nw) mk5 = __ldg(mrow + 5);
+            if (6 < nw) mk6 = __ldg(mrow + 6);
+            if (7 < nw) mk7 = __ldg(mrow + 7);
+          }
+        }
+        if (EPI == 3 && row_ok) rstat = p.rowstat[static_cast<size_t>(tc.b) * p.M + row0 + lane];
+      }
+      mbar_wait(&tfull_bar[acc], acc_phase);
+      tc_fence_after();
       const bool tn_remote = (OP == DDP_OP_TN) && dist;
       if (tn_remote && tc.seg != p.rank && !(done_ok & (1u << tc.seg))) {
         if (lane == 0) wait_flag_ge(p.done[p.rank] + tc.seg, p.seq - 2u, p.status, 4);
@@ -421,35 +501,155 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
         done_ok |= 1u << tc.seg;
       }
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
+      if constexpr (EPI == 2) {
+        // ---- statistics pass: nothing is stored but (max, sum) of this row over the tile's columns
+        float m_run = -INFINITY, l_run = 0.f;
+#pragma unroll 1
+        for (int c0 = ch * CW; c0 < (ch + 1) * CW; c0 += 32) {
+          if (n0 + c0 >= p.N) break;
+          uint32_t r[32];
+          tmem_ld_32x32(taddr + c0, r);
+          tmem_ld_wait();
+          tmem_ld_pin(r);
+          const uint32_t mb = pick8(mk0, mk1, mk2, mk3, mk4, mk5, mk6, mk7, c0 >> 5);
+          const int nvalid = min(32, p.N - (n0 + c0));
+          float tv[32];
+          float cmax = -INFINITY;
+          if (nvalid == 32 && !__any_sync(0xffffffffu, mb != 0u)) {
+            // common case (no mask bit anywhere in these 32 x 32 scores): max of the raw accumulators
+#pragma unroll
+            for (int e = 0; e < 32; ++e) {
+              tv[e] = __uint_as_float(r[e]);
+              cmax = fmaxf(cmax, tv[e]);
+            }
+            cmax *= p.epi_scale;  // epi_scale > 0
+            const float m_new = fmaxf(m_run, cmax);
+            float acc_l = 0.f;
+#pragma unroll
+            for (int e = 0; e < 32; ++e) acc_l += ex2_approx(fmaf(tv[e], p.epi_scale, -m_new));
+            l_run = l_run * ex2_approx(m_run - m_new) + acc_l;
+            m_run = m_new;
+          } else {
+#pragma unroll
+            for (int e = 0; e < 32; ++e) {
+              const bool dead = ((mb >> e) & 1u) || e >= nvalid;
+              tv[e] = dead ? -INFINITY : __uint_as_float(r[e]) * p.epi_scale;
+              cmax = fmaxf(cmax, tv[e]);
+            }
+            const float m_new = fmaxf(m_run, cmax);
+            if (m_new != -INFINITY) {
+              float acc_l = 0.f;
+#pragma unroll
+              for (int e = 0; e < 32; ++e) acc_l += ex2_approx(tv[e] - m_new);
+              l_run = l_run * ex2_approx(m_run - m_new) + acc_l;
+              m_run = m_new;
+            }
+          }
+        }
+        if (row0 + lane < p.M) {
+          const int ti = (tc.seg * p.n_blocks + n0 / BN) * (EW / 4) + ch;
+          p.stats[(static_cast<size_t>(tc.b) * p.M + row0 + lane) * p.stats_nt + ti] = make_float2(m_run, l_run);
+        }
+      }
       // Drains the accumulator in chunks of 128 output bytes per row (64 bf16/fp16 or 32 fp32 columns).
       auto drain = [&](auto tag, bool to_peer) {
         using StoreT = decltype(tag);
         constexpr int CC = 128 / sizeof(StoreT);
         constexpr int NLD = CC / 32;
 #pragma unroll 1
-        for (int c0 = 0; c0 < BN; c0 += CC) {
+        for (int c0 = ch * CW; c0 < (ch + 1) * CW; c0 += CC) {
           const int col0 = n0 + c0;
           const int cols_valid = min(CC, p.N - col0);
-          if (cols_valid <= 0 || rows_valid == 0) break;  // warp-uniform
-          uint32_t r[NLD][32];
-#pragma unroll
-          for (int i = 0; i < NLD; ++i) tmem_ld_32x32(taddr + c0 + i * 32, r[i]);
-          tmem_ld_wait();
-          float v[CC];
-#pragma unroll
-          for (int i = 0; i < NLD; ++i)
-#pragma unroll
-            for (int e = 0; e < 32; ++e) v[i * 32 + e] = __uint_as_float(r[i][e]) * p.alpha;
-          if (!to_peer && p.bias != nullptr) {
-            const StoreT* bias = reinterpret_cast<const StoreT*>(p.bias);
-#pragma unroll
-            for (int e = 0; e < CC; ++e)
-              if (e < cols_valid) v[e] += static_cast<float>(bias[col0 + e]);
+          const bool active = cols_valid > 0 && rows_valid > 0;  // warp-uniform
+          const char* pbuf = pbuf0 + (g % kPBufs) * 4096;
+          if constexpr (EPI == 1) {
+            if (!to_peer) {
+              if (lane == 0) issue_p(g + kPBufs - 1);              // its buffer was drained one chunk ago
+              mbar_wait(&p_bar[q * kPBufs + (g % kPBufs)], (g / kPBufs) & 1);  // every chunk is loaded, used or not
+              ++g;
+            }
           }
-          char* sbuf = sbuf0 + sb * 4096;
+          if (!active) {
+            if (EPI == 1) continue;
+            break;
+          }
+          // TMEM -> registers.  With two epilogue warps per lane quadrant (EW == 8) only ONE 32-column load
+          // per warp is kept in flight: more than two outstanding 32x32b.x32 loads on a quadrant returned
+          // zeros for the oldest one on B200 (observed, intermittent), so those loads are issued per part.
+          uint32_t r[NLD][32];
+          if constexpr (EW == 4) {
+            if constexpr (NLD == 2) {
+              tmem_ld_32x64(taddr + c0, reinterpret_cast<uint32_t(&)[64]>(r));
+            } else {
+              tmem_ld_32x32(taddr + c0, r[0]);
+            }
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < NLD; ++i) tmem_ld_pin(r[i]);
+          }
+          if (p.dbg & 4) continue;  // harness only: time the TMEM drain alone
+          const uint32_t sbuf = smem_u32(sbuf0) + sb * 4096;  // shared-space address of this chunk's buffer
           if (lane == 0) bulk_wait_group_read<1>();  // the TMA store that last read this buffer is done
           __syncwarp();
-          stage_row<StoreT, CC>(sbuf, lane, v);
+          // 32 columns at a time: registers -> epilogue math -> this row's slice of the staging tile
+#pragma unroll
+          for (int i = 0; i < NLD; ++i) {
+            if constexpr (EW == 8) {
+              tmem_ld_32x32(taddr + c0 + i * 32, r[i]);
+              tmem_ld_wait();
+              tmem_ld_pin(r[i]);
+            }
+            float v[32];
+#pragma unroll
+            for (int e = 0; e < 32; ++e) v[e] = __uint_as_float(r[i][e]) * p.alpha;
+            if (p.dbg & 64) {  // harness: marker values instead of the accumulator (tests the store path alone)
+#pragma unroll
+              for (int e = 0; e < 32; ++e) v[e] = static_cast<float>(c0 + i * 32 + e);
+            }
+            if (EPI == 3 && !(p.dbg & 32)) {  // dbg 32 (harness): store the raw scores instead
+              // P = exp2(scale*log2e*s - (row max + log2 row sum)); masked entries are exactly 0 and a fully
+              // masked row (rstat.x = NaN) is NaN, as softmax over a row of -inf is in the reference
+              const uint32_t cw = pick8(mk0, mk1, mk2, mk3, mk4, mk5, mk6, mk7, (c0 >> 5) + i);
+              const float neg_x = -rstat.x;
+              if (!__any_sync(0xffffffffu, cw != 0u)) {
+#pragma unroll
+                for (int e = 0; e < 32; ++e) v[e] = ex2_approx(fmaf(v[e], p.epi_scale, neg_x));
+              } else {
+                const float dead_t = (rstat.x == rstat.x) ? -INFINITY : rstat.x;
+#pragma unroll
+                for (int e = 0; e < 32; ++e)
+                  v[e] = ex2_approx(((cw >> e) & 1u) ? dead_t : fmaf(v[e], p.epi_scale, neg_x));
+              }
+            }
+            if constexpr (EPI == 1) {
+              if (!to_peer) {
+                // dS = scale * P * (dP - delta): P row of this thread from the swizzled landing buffer
+                constexpr int VE = 16 / sizeof(StoreT);
+                constexpr int VPP = 32 / VE;  // 16-byte vectors per 32 columns
+#pragma unroll
+                for (int j = 0; j < VPP; ++j) {
+                  const int jj = i * VPP + j;
+                  const uint4 pv = ld_shared_v4(smem_u32(pbuf) + lane * 128 + ((jj ^ (lane & 7)) * 16));
+                  const StoreT* pe = reinterpret_cast<const StoreT*>(&pv);
+#pragma unroll
+                  for (int e = 0; e < VE; ++e)
+                    v[j * VE + e] = p.epi_scale * static_cast<float>(pe[e]) * (v[j * VE + e] - row_delta);
+                }
+              }
+            }
+            if (!to_peer && p.bias != nullptr) {
+              const StoreT* bias = reinterpret_cast<const StoreT*>(p.bias);
+#pragma unroll
+              for (int e = 0; e < 32; ++e)
+                if (i * 32 + e < cols_valid) v[e] += static_cast<float>(bias[col0 + i * 32 + e]);
+            }
+            stage_row32<StoreT>(sbuf, lane, v, i);
+          }
+          if (p.dbg & 8) {  // harness only: no store
+            __syncwarp();
+            sb ^= 1;
+            continue;
+          }
           if (to_peer) {
             // fp32 partial tile -> owner's slot [src = rank][b][M][N]
             __syncwarp();
@@ -477,7 +677,9 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
           sb ^= 1;
         }
       };
-      if (tn_remote) {
+      if (EPI == 2) {
+        // statistics only
+      } else if (tn_remote) {
         drain(float{}, true);
       } else {
         drain(OutT{}, false);

@@ -433,3 +433,74 @@ extern "C" int ddp_rowdot(const ddp_tensor* a, const ddp_tensor* b, float* out, 
   }
   return cuda_check(cudaGetLastError(), "rowdot launch");
 }
+
+// ---------------------------------------------------------------------------------------------------------
+// Helpers of the fused softmax-forward path (ddp_gemm_ex with DDP_EPI_SOFTMAX_STATS / _APPLY).
+namespace ddp {
+
+// One thread packs 32 mask bytes (two 16-byte loads when aligned) into one word; bits past the row end read
+// as "masked".
+__global__ void pack_mask_kernel(const uint8_t* __restrict__ mask, long long rows_total, long long rows, long long cols,
+                                 long long m_ld, long long m_sb1, uint32_t* __restrict__ bits, long long ld_words) {
+  const long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (idx >= rows_total * ld_words) return;
+  const long long r = idx / ld_words, w = idx - r * ld_words;
+  const long long b1i = r / rows, row = r - b1i * rows;
+  const uint8_t* src = mask + b1i * m_sb1 + row * m_ld + w * 32;
+  uint32_t word = 0;
+  if (w * 32 + 32 <= cols && (reinterpret_cast<uintptr_t>(src) & 15) == 0) {
+    const uint4 a = *reinterpret_cast<const uint4*>(src);
+    const uint4 b = *reinterpret_cast<const uint4*>(src + 16);
+    const uint32_t v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        if ((v[i] >> (8 * k)) & 0xffu) word |= 1u << (4 * i + k);
+  } else {
+    for (int k = 0; k < 32; ++k) {
+      const long long c = w * 32 + k;
+      if (c >= cols || src[k] != 0) word |= 1u << k;
+    }
+  }
+  bits[idx] = word;
+}
+
+// One thread per row: fold the per-tile (max, sum) pairs.
+__global__ void softmax_combine_kernel(const float2* __restrict__ stats, long long n_rows, int nt,
+                                       float2* __restrict__ rowstat) {
+  const long long r = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (r >= n_rows) return;
+  const float2* s = stats + r * nt;
+  float m = -INFINITY;
+  for (int t = 0; t < nt; ++t) m = fmaxf(m, s[t].x);
+  float l = 0.f;
+  for (int t = 0; t < nt; ++t) {
+    const float2 v = s[t];
+    if (v.x != -INFINITY) l += v.y * exp2f(v.x - m);
+  }
+  // rowstat.x = max + log2(sum): P = exp2(t - rowstat.x) needs no separate division.  A fully masked row
+  // gets NaN -> NaN probabilities, like softmax over a row of -inf in the reference.
+  rowstat[r] = (m == -INFINITY) ? make_float2(__int_as_float(0x7fc00000), 0.f) : make_float2(m + log2f(l), 1.f / l);
+}
+
+}  // namespace ddp
+
+extern "C" int ddp_pack_mask(const uint8_t* mask, int64_t b1, int64_t rows, int64_t cols, int64_t mask_ld,
+                             int64_t mask_sb1, uint32_t* bits, int64_t ld_words, void* stream) {
+  const long long total_words = b1 * rows * ld_words;
+  const int threads = 256;
+  const long long blocks = (total_words + threads - 1) / threads;
+  if (blocks > 0x7fffffffLL) return ddp::set_error(-4, "pack_mask: mask too large");
+  ddp::pack_mask_kernel<<<static_cast<unsigned>(blocks), threads, 0, static_cast<cudaStream_t>(stream)>>>(
+      mask, b1 * rows, rows, cols, mask_ld, mask_sb1, bits, ld_words);
+  return ddp::cuda_check(cudaGetLastError(), "pack_mask launch");
+}
+
+extern "C" int ddp_softmax_combine(const void* stats, int64_t n_rows, int32_t nt, void* rowstat, void* stream) {
+  const int threads = 128;
+  const long long blocks = (n_rows + threads - 1) / threads;
+  ddp::softmax_combine_kernel<<<static_cast<unsigned>(blocks), threads, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const float2*>(stats), n_rows, nt, static_cast<float2*>(rowstat));
+  return ddp::cuda_check(cudaGetLastError(), "softmax_combine launch");
+}

@@ -239,7 +239,7 @@ static bool run_case(const Case& c, int dbg, bool verbose) {
   return ok;
 }
 
-static void perf_case(int op, int dt, int b0, int M, int Tn, int D, int iters) {
+static void perf_case(int op, int dt, int b0, int M, int Tn, int D, int iters, int dbg = 0) {
   const int es = esize(dt);
   HT A, B, C;
   if (op == DDP_OP_NT) {
@@ -266,13 +266,13 @@ static void perf_case(int op, int dt, int b0, int M, int Tn, int D, int iters) {
   CK(cudaEventCreate(&e0));
   CK(cudaEventCreate(&e1));
   for (int i = 0; i < 3; ++i)
-    if (ddp_gemm(op, &a, &b, &c, 1.f, nullptr, nullptr, 0, 0)) {
+    if (ddp_gemm(op, &a, &b, &c, 1.f, nullptr, nullptr, dbg, 0)) {
       printf("perf launch failed: %s\n", ddp_last_error());
       return;
     }
   CK(cudaDeviceSynchronize());
   CK(cudaEventRecord(e0));
-  for (int i = 0; i < iters; ++i) ddp_gemm(op, &a, &b, &c, 1.f, nullptr, nullptr, 0, 0);
+  for (int i = 0; i < iters; ++i) ddp_gemm(op, &a, &b, &c, 1.f, nullptr, nullptr, dbg, 0);
   CK(cudaEventRecord(e1));
   CK(cudaEventSynchronize(e1));
   float ms;
@@ -289,7 +289,7 @@ static void perf_case(int op, int dt, int b0, int M, int Tn, int D, int iters) {
   }
   (void)rowsA;
   bytes = (double)(A.size() + B.size() + C.size()) * es;
-  printf("PERF %s %s b0=%d M=%d Tn=%d D=%d: %.3f ms  %.1f TFLOP/s  %.1f GB/s (algorithmic)\n", opname(op), dtname(dt),
+  printf("PERF dbg=%d %s %s b0=%d M=%d Tn=%d D=%d: %.3f ms  %.1f TFLOP/s  %.1f GB/s (algorithmic)\n", dbg, opname(op), dtname(dt),
          b0, M, Tn, D, ms, flops / ms * 1e-9, bytes / ms * 1e-6);
   fflush(stdout);
   cudaFree(dA); cudaFree(dB); cudaFree(dC);
@@ -351,6 +351,14 @@ int main(int argc, char** argv) {
       }
     }
     printf("SUMMARY pass=%d fail=%d\n", g_pass, g_fail);
+  }
+  if (mode == "epi") {
+    perf_case(DDP_OP_NT, DDP_BF16, 16, 8192, 8192, 64, 10, 0);
+    perf_case(DDP_OP_NT, DDP_BF16, 16, 8192, 8192, 64, 10, 4);
+    perf_case(DDP_OP_NT, DDP_BF16, 16, 8192, 8192, 64, 10, 8);
+    perf_case(DDP_OP_NT, DDP_F32, 16, 8192, 8192, 64, 10, 0);
+    perf_case(DDP_OP_NT, DDP_F32, 16, 8192, 8192, 64, 10, 4);
+    perf_case(DDP_OP_NT, DDP_F32, 16, 8192, 8192, 64, 10, 8);
   }
   if (mode == "perf" || mode == "full") {
     // flagship per-rank shapes at world 1 (T = 8192) and compute-bound shapes

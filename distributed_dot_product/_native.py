@@ -33,6 +33,15 @@ class Comm(ctypes.Structure):
                 ('status', ctypes.c_void_p)]
 
 
+class Epilogue(ctypes.Structure):
+    _fields_ = [('mode', ctypes.c_int32), ('scale', ctypes.c_float), ('P', ctypes.POINTER(Tensor)),
+                ('delta', ctypes.c_void_p), ('mask_bits', ctypes.c_void_p), ('mask_ld_words', ctypes.c_int64),
+                ('mask_sb1_words', ctypes.c_int64), ('stats', ctypes.c_void_p), ('rowstat', ctypes.c_void_p)]
+
+
+EPI_NONE, EPI_SOFTMAX_BWD, EPI_SOFTMAX_STATS, EPI_SOFTMAX_APPLY = 0, 1, 2, 3
+
+
 class NativeError(RuntimeError):
     pass
 
@@ -67,6 +76,12 @@ def load():
                                            c.POINTER(c.c_size_t)]
         lib.ddp_gemm.argtypes = [c.c_int, tp, tp, tp, c.c_float, c.c_void_p, c.POINTER(Comm), c.c_int,
                                  c.c_void_p]
+        lib.ddp_gemm_ex.argtypes = [c.c_int, tp, tp, tp, c.c_float, c.c_void_p, c.POINTER(Comm),
+                                    c.POINTER(Epilogue), c.c_int, c.c_void_p]
+        lib.ddp_gemm_stats_tiles.argtypes = [tp, tp, c.c_int]
+        lib.ddp_pack_mask.argtypes = [c.c_void_p, c.c_int64, c.c_int64, c.c_int64, c.c_int64, c.c_int64, c.c_void_p,
+                                      c.c_int64, c.c_void_p]
+        lib.ddp_softmax_combine.argtypes = [c.c_void_p, c.c_int64, c.c_int32, c.c_void_p, c.c_void_p]
         lib.ddp_softmax_fwd.argtypes = [tp, tp, c.c_void_p, c.c_int64, c.c_int64, c.c_float, c.c_void_p]
         lib.ddp_softmax_bwd.argtypes = [tp, tp, tp, c.c_void_p, c.c_float, c.c_void_p]
         lib.ddp_rowdot.argtypes = [tp, tp, c.c_void_p, c.c_void_p]

@@ -13,6 +13,8 @@ import torch
 from distributed_dot_product import _native
 from distributed_dot_product.parallel import runtime
 
+import os as _os
+_DBG = int(_os.environ.get('DDP_GEMM_DBG', '0'))  # kernel debug bits (see ddp_gemm); 0 in production
 _DT = {torch.float16: _native.F16, torch.bfloat16: _native.BF16, torch.float32: _native.F32}
 
 
@@ -126,11 +128,13 @@ def _gemm_padded_segments(op, left, right, offset, out, alpha, world, seg, q, in
     return res
 
 
-def gemm(op, left, right, offset=32, out=None, alpha=1.0, bias=None, distributed=True):
+def gemm(op, left, right, offset=32, out=None, alpha=1.0, bias=None, distributed=True, softmax_bwd=None,
+         epilogue_builder=None):
     """Runs one fused product.  ``left``/``right`` follow the reference shapes
     (functions.py:44-212).  ``out`` may be a preallocated, possibly strided result tensor (e.g. the
     ``[B, H, Tn, d]`` view of a ``[B, Tn, H*d]`` buffer): the kernel then writes the final layout
-    directly."""
+    directly.  ``softmax_bwd=(P, delta, scale)`` (nt only) fuses the softmax backward into the epilogue:
+    the result is ``scale * P * (left @ gather(right)^T - delta[..., None])``."""
     lib = _native.load()
     world = runtime.get_world_size() if distributed else 1
     in_dtype = left.dtype
@@ -185,8 +189,23 @@ def gemm(op, left, right, offset=32, out=None, alpha=1.0, bias=None, distributed
         if bias.dtype != cdt or not bias.is_contiguous():
             bias = bias.to(cdt).contiguous()
         bias_ptr = ctypes.c_void_p(bias.data_ptr())
-    _native.check(lib.ddp_gemm(op, ctypes.byref(va), ctypes.byref(vb), ctypes.byref(vc), float(alpha), bias_ptr,
-                               comm_ptr, 0, _stream()))
+    epi_ptr = None
+    if softmax_bwd is not None:
+        probs, delta, scale = softmax_bwd
+        p4 = _unsqueeze4(probs)
+        if p4.dim() != 4 or not _aligned(p4) or tuple(p4.shape) != tuple(c4.shape) or p4.dtype != cdt:
+            raise ValueError('softmax_bwd: P must be a TMA-addressable tensor with the shape of the result')
+        vp = as_view(p4)
+        epi = _native.Epilogue()
+        epi.mode, epi.scale = _native.EPI_SOFTMAX_BWD, float(scale)
+        epi.P = ctypes.pointer(vp)
+        epi.delta = delta.data_ptr()
+        epi_ptr = ctypes.byref(epi)
+    elif epilogue_builder is not None:
+        epi = epilogue_builder(va, vb, vc, world)   # returns a filled _native.Epilogue
+        epi_ptr = ctypes.byref(epi)
+    _native.check(lib.ddp_gemm_ex(op, ctypes.byref(va), ctypes.byref(vb), ctypes.byref(vc), float(alpha), bias_ptr,
+                                  comm_ptr, epi_ptr, _DBG, _stream()))
     _native.count_launch()
     if direct:
         return out

@@ -72,6 +72,37 @@ int ddp_gemm_workspace(int op, const ddp_tensor* A, const ddp_tensor* B, int wor
 int ddp_gemm(int op, const ddp_tensor* A, const ddp_tensor* B, const ddp_tensor* C, float alpha,
              const void* bias, const ddp_comm* comm, int dbg, void* stream);
 
+/* ddp_gemm with a fused epilogue.  DDP_EPI_SOFTMAX_BWD (nt only) turns the dP = dO . gather(V)^T product of
+ * the attention backward into dS directly:  C = scale * P * (alpha * A.B^T - delta[row]),  with P the saved
+ * probabilities (same shape, dtype and batch layout as C; P tiles are TMA-prefetched into the epilogue) and
+ * delta[b1][b0][rows] = rowsum(dO * O) in fp32 - the softmax backward (autograd of module.py:65-67) without a
+ * separate pass over the slab. */
+enum { DDP_EPI_NONE = 0, DDP_EPI_SOFTMAX_BWD = 1, DDP_EPI_SOFTMAX_STATS = 2, DDP_EPI_SOFTMAX_APPLY = 3 };
+/* DDP_EPI_SOFTMAX_STATS / _APPLY (nt only) fuse module.py:65-67 (scale, masked_fill, softmax) into the
+ * K.gather(Q)^T product so that the score slab never exists: the STATS launch stores, per row and column tile,
+ * the online-softmax (max, sum) of scale*log2(e)*scores into stats[b1][b0][rows][ddp_gemm_stats_tiles()] and
+ * writes nothing else; ddp_softmax_combine folds them into rowstat[b1][b0][rows] = (row max, 1/row sum); the
+ * APPLY launch recomputes the tiles and writes C = exp2(t - max) / sum directly.  mask_bits is the mask packed
+ * by ddp_pack_mask (bit set = masked out; NULL = no mask). */
+typedef struct ddp_epilogue {
+  int32_t mode;
+  float scale;
+  const ddp_tensor* P;       /* SOFTMAX_BWD */
+  const float* delta;        /* SOFTMAX_BWD */
+  const uint32_t* mask_bits; /* SOFTMAX_STATS / APPLY */
+  int64_t mask_ld_words, mask_sb1_words;
+  void* stats;               /* SOFTMAX_STATS out: float2 */
+  const void* rowstat;       /* SOFTMAX_APPLY in: float2 */
+} ddp_epilogue;
+int ddp_gemm_stats_tiles(const ddp_tensor* A, const ddp_tensor* B, int world);
+/* bits[b1][rows][ld_words] <- mask u8 [b1][rows][cols] (nonzero = masked); bits past `cols` are set. */
+int ddp_pack_mask(const uint8_t* mask, int64_t b1, int64_t rows, int64_t cols, int64_t mask_ld, int64_t mask_sb1,
+                  uint32_t* bits, int64_t ld_words, void* stream);
+/* rowstat[r] = (max_t m, 1 / sum_t l * exp2(m_t - max)) over the nt column tiles of row r; n_rows = b1*b0*rows. */
+int ddp_softmax_combine(const void* stats, int64_t n_rows, int32_t nt, void* rowstat, void* stream);
+int ddp_gemm_ex(int op, const ddp_tensor* A, const ddp_tensor* B, const ddp_tensor* C, float alpha,
+                const void* bias, const ddp_comm* comm, const ddp_epilogue* epi, int dbg, void* stream);
+
 /* Row softmax over the last dim of x[b1][b0][rows][cols] with fused scale and boolean mask:
  *   y = softmax(scale * x  masked_fill(mask, -inf))     (reference: module.py:65-67)
  * mask is uint8 [b1][rows][cols] (broadcast over b0 = heads), nonzero = masked out; may be NULL.

@@ -223,3 +223,56 @@ def test_colsum_row_split(cuda_device, dtype, rows, cols):
     tol = 1e-3 if dtype == torch.float32 else 1.0
     assert got.dtype == dtype
     assert (got.float() - want).abs().max().item() <= tol * max(1.0, want.abs().max().item() / 64)
+
+
+@pytest.mark.parametrize('dtype', [torch.bfloat16, torch.float32])
+@pytest.mark.parametrize('shape', [(2, 3, 200, 64), (1, 2, 130, 40)])
+def test_fused_softmax_backward_epilogue(cuda_device, dtype, shape):
+    """nt product with the softmax backward fused into its epilogue vs the unfused composition."""
+    from distributed_dot_product import _native
+    import distributed_dot_product.ops.gemm as G
+    torch.manual_seed(9)
+    b, h, t, d = shape
+    g = torch.randn(b, h, t, d, device=cuda_device).to(dtype)
+    v = torch.randn(b, h, t, d, device=cuda_device).to(dtype)
+    tpad = (t + 7) // 8 * 8  # P rows must be 16-byte aligned, as the slab produced by the nt kernel is
+    probs = torch.zeros(b, h, t, tpad, device=cuda_device, dtype=dtype)[..., :t]
+    probs.copy_(torch.softmax(torch.randn(b, h, t, t, device=cuda_device), -1))
+    delta = torch.randn(b, h, t, device=cuda_device)
+    scale = 0.3
+    got = G.gemm(_native.OP_NT, g, v, softmax_bwd=(probs, delta, scale))
+    dp = g.float() @ v.float().transpose(-1, -2)
+    want = scale * probs.float() * (dp - delta.unsqueeze(-1))
+    tol = 2e-3 if dtype == torch.float32 else 3e-2
+    assert (got.float() - want).abs().max().item() <= tol * max(1.0, want.abs().max().item())
+
+
+@pytest.mark.parametrize('dtype', [torch.bfloat16, torch.float32])
+@pytest.mark.parametrize('shape,masked', [((2, 3, 200, 64), True), ((1, 2, 130, 40), True), ((1, 4, 600, 32), False)])
+def test_fused_softmax_forward_epilogue(cuda_device, dtype, shape, masked):
+    """softmax(scale * K Q^T masked) from the two-pass fused nt kernels vs plain PyTorch."""
+    from distributed_dot_product.ops.attention import fused_softmax_nt
+    torch.manual_seed(10)
+    b, h, t, d = shape
+    k = torch.randn(b, h, t, d, device=cuda_device).to(dtype)
+    q = torch.randn(b, h, t, d, device=cuda_device).to(dtype)
+    mask = None
+    if masked:
+        mask = torch.rand(b, t, t, device=cuda_device) < 0.4
+        mask[..., 0] = False
+        mask[0, 5] = True          # a fully masked row -> NaN, like the reference
+    scale = 0.21
+    got = fused_softmax_nt(k, q, mask, scale, 64)
+    s = (k.float() @ q.float().transpose(-1, -2)) * scale
+    if masked:
+        s = s.masked_fill(mask.unsqueeze(1), -float('inf'))
+    want = torch.softmax(s, -1)
+    if masked:
+        assert torch.isnan(got[0, :, 5]).all()
+        got = got.clone()
+        got[0, :, 5] = 0
+        want[0, :, 5] = 0
+    tol = 2e-3 if dtype == torch.float32 else 1e-2
+    assert got.dtype == dtype and got.shape == want.shape
+    assert (got.float() - want).abs().max().item() < tol
+    assert (got.float().sum(-1)[want.sum(-1) > 0] - 1).abs().max().item() < (1e-3 if dtype == torch.float32 else 2e-2)
