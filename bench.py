@@ -246,6 +246,7 @@ def main():
             'e2e': {'value': ms_e2e, 'unit': 'ms', 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': 4},
             'gpu_launches': launches if launches is not None else 0,
             'loss': float(loss_host.item()),
+            'peak_mem_gb': torch.cuda.max_memory_allocated() / 1e9,
         })
         if reference:
             result['gpu_launches_note'] = 'reference arm: library kernels only (cuBLAS/ATen/NCCL)'
