@@ -13,6 +13,10 @@
 //   OP_TN  P_dest[m, n]   = A[k, dest*M + m]^T . B[k, n]           A MN-major, B MN-major
 // "seg" walks the ranks in rank-rotated order (own block first for NT/NN, last for TN).
 #pragma once
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+
+#include <type_traits>
 #include "../common/ptx.cuh"
 #include "../../include/ddp_b200.h"
 
@@ -621,7 +625,38 @@ __global__ void __launch_bounds__(kThreadsBase + 32 * EW, 1) gemm_kernel(const _
                   v[e] = ex2_approx(((cw >> e) & 1u) ? dead_t : fmaf(v[e], p.epi_scale, neg_x));
               }
             }
-            if constexpr (EPI == 1) {
+            if constexpr (EPI == 1 && sizeof(StoreT) == 2) {
+              if (!to_peer) {
+                // dS = P * (scale*dP - scale*delta) with P kept packed: one fp32 FMA per element, then the
+                // product in packed 16-bit math straight into the staging tile (P never gets unpacked).
+                using P2 = typename std::conditional<std::is_same<StoreT, __half>::value, __half2, __nv_bfloat162>::type;
+                const float nsd = -p.epi_scale * row_delta;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                  const int jj = i * 4 + j;
+                  const uint32_t slot = lane * 128 + ((jj ^ (lane & 7)) * 16);
+                  const uint4 pv = ld_shared_v4(smem_u32(pbuf) + slot);
+                  const P2* pp = reinterpret_cast<const P2*>(&pv);
+                  uint4 ov;
+                  P2* op = reinterpret_cast<P2*>(&ov);
+#pragma unroll
+                  for (int e = 0; e < 4; ++e) {
+                    P2 t;
+                    if constexpr (std::is_same<StoreT, __half>::value) {
+                      t = __floats2half2_rn(fmaf(v[j * 8 + 2 * e], p.epi_scale, nsd),
+                                            fmaf(v[j * 8 + 2 * e + 1], p.epi_scale, nsd));
+                    } else {
+                      t = __floats2bfloat162_rn(fmaf(v[j * 8 + 2 * e], p.epi_scale, nsd),
+                                                fmaf(v[j * 8 + 2 * e + 1], p.epi_scale, nsd));
+                    }
+                    op[e] = __hmul2(t, pp[e]);
+                  }
+                  st_shared_v4(sbuf + slot, ov);
+                }
+                continue;  // this part is staged
+              }
+            }
+            if constexpr (EPI == 1 && sizeof(StoreT) == 4) {
               if (!to_peer) {
                 // dS = scale * P * (dP - delta): P row of this thread from the swizzled landing buffer
                 constexpr int VE = 16 / sizeof(StoreT);
