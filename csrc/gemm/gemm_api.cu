@@ -38,6 +38,14 @@ static int make_map(CUtensorMap* m, int dt, void* ptr, const uint64_t dims[5], c
                     const uint32_t box[5], bool mn_major) {
   EncodeFn enc = get_encode_fn();
   if (!enc) return set_error(-10, "cuTensorMapEncodeTiled is not available from the driver");
+  // The encoder is a driver-API call and needs a current context on THIS thread.  A fresh thread (e.g. the
+  // autograd engine's worker when our node is the first CUDA work it sees) has none until a runtime call
+  // binds the primary context: do that once per thread.
+  static thread_local bool ctx_bound = false;
+  if (!ctx_bound) {
+    cudaFree(nullptr);
+    ctx_bound = true;
+  }
   if (reinterpret_cast<uintptr_t>(ptr) & 15) return set_error(-2, "tensor base address is not 16-byte aligned");
   cuuint64_t gd[5], gs[4];
   cuuint32_t bx[5], es[5] = {1, 1, 1, 1, 1};

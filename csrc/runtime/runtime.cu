@@ -68,3 +68,7 @@ extern "C" int ddp_heap_free(void* ptr) { return cuda_check(cudaFree(ptr), "cuda
 extern "C" int ddp_memset_async(void* ptr, int value, size_t bytes, void* stream) {
   return cuda_check(cudaMemsetAsync(ptr, value, bytes, static_cast<cudaStream_t>(stream)), "cudaMemsetAsync");
 }
+
+extern "C" int ddp_read_u32(const void* dev_ptr, uint32_t* out) {
+  return cuda_check(cudaMemcpy(out, dev_ptr, sizeof(uint32_t), cudaMemcpyDeviceToHost), "cudaMemcpy(status word)");
+}

@@ -211,3 +211,25 @@ class _Heap(object):
 def heap():
     init()
     return _Heap.get()
+
+
+def check_status():
+    """Failure detection: raises if a fused kernel on this rank ever gave up waiting for a peer.
+
+    The kernels never hang the GPU: a wait on a peer flag that exceeds 20 s records which wait it was
+    (1/2 = gathered rows for nt/all, 3/4 = a peer's done counter, 5 = reduce-scatter partials) in a sticky
+    status word of the symmetric heap and carries on with invalid data.  Call this (it synchronises the
+    device) at step boundaries of long jobs, or after an unexpected result, to turn that into an exception.
+    """
+    hp = _Heap._instance
+    if hp is None or hp.base is None:
+        return 0
+    torch.cuda.synchronize()
+    lib = _native.load()
+    host = ctypes.c_uint32(0)
+    rc = lib.ddp_read_u32(ctypes.c_void_p(hp.base + 384), ctypes.byref(host))
+    _native.check(rc)
+    if host.value:
+        raise RuntimeError('distributed-dot-product: a fused kernel timed out waiting for a peer '
+                           '(wait id %d); results since then are invalid' % host.value)
+    return 0

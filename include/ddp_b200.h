@@ -147,6 +147,8 @@ int ddp_heap_open(const void* ipc_handle64, void** ptr);
 int ddp_heap_close(void* ptr);
 int ddp_heap_free(void* ptr);
 int ddp_memset_async(void* ptr, int value, size_t bytes, void* stream);
+/* Synchronous read of one device word (the sticky status word of ddp_comm). */
+int ddp_read_u32(const void* dev_ptr, uint32_t* out);
 
 #ifdef __cplusplus
 }

@@ -276,3 +276,15 @@ def test_fused_softmax_forward_epilogue(cuda_device, dtype, shape, masked):
     assert got.dtype == dtype and got.shape == want.shape
     assert (got.float() - want).abs().max().item() < tol
     assert (got.float().sum(-1)[want.sum(-1) > 0] - 1).abs().max().item() < (1e-3 if dtype == torch.float32 else 2e-2)
+
+
+def test_backward_first_cuda_work_on_autograd_thread(cuda_device):
+    """The autograd worker thread may reach our kernels before any other CUDA call bound a context to it
+    (TMA descriptor encoding is a driver-API call): run backward with our node first in a fresh process."""
+    code = (
+        "import torch, sys; sys.path.insert(0, %r);"
+        "from distributed_dot_product.multiplication.ops import RightTransposeMultiplication as R;"
+        "a = torch.rand(1, 256, 64, device='cuda', requires_grad=True);"
+        "out = R.apply(a, a, 64); out.backward(torch.ones_like(out)); torch.cuda.synchronize(); print('ok')" % ROOT)
+    r = subprocess.run(['python', '-c', code], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300)
+    assert r.returncode == 0 and 'ok' in r.stdout, r.stdout[-2000:]
