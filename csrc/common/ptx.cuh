@@ -57,8 +57,27 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+// Last pipeline wait that gave up (0 = none): see mbar_wait.  Read and cleared by ddp_debug_timeout_site().
+__device__ unsigned int g_ddp_timeout_site = 0;
+
+// Spins on an mbarrier phase.  A pipeline bug must not hang the GPU (and whoever shares it): after ~4 s of
+// spinning the wait gives up, records which wait it was (`site`) and returns; the kernel then finishes with
+// invalid results and the host can tell through ddp_debug_timeout_site().
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, uint32_t site = 99) {
+  if (mbar_try_wait(bar, parity)) return;
+  uint64_t t0 = 0;
+  uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
+    if ((++spins & 0xFFFu) == 0) {
+      uint64_t now;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+      if (t0 == 0) {
+        t0 = now;
+      } else if (now - t0 > 4000000000ull) {
+        atomicMax(&g_ddp_timeout_site, site);
+        return;
+      }
+    }
   }
 }
 

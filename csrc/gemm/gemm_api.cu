@@ -81,18 +81,20 @@ static int make_map(CUtensorMap* m, int dt, void* ptr, const uint64_t dims[5], c
   return 0;
 }
 
-template <int OP, int DT, int BN, int EPI>
+template <int OP, int DT, int BN, int EPI, int EWX = 0>
 static int launch_one(const GemmKParams& p, int grid, cudaStream_t stream) {
   // The exp-heavy softmax statistics epilogue runs on 8 epilogue warps (two per TMEM lane quadrant).
   // (The store path of the 8-warp configuration is not enabled: on B200 the second warp of a quadrant
-  //  intermittently drained zeros for its first 32 columns after a TMA store; see DESIGN.md.)
-  constexpr int EW = (EPI == 2) ? 8 : 4;
+  //  intermittently drained zeros for its first 32 columns after a TMA store; see DESIGN.md.  dbg bit 128
+  //  selects it for experiments.)
+  // (two warps per quadrant split a tile's columns, so the tile must hold at least two 128-byte chunks per row)
+  constexpr int EW = ((EPI == 1 || EPI == 2 || EWX == 8) && BN >= 128) ? 8 : 4;
   // smem ring depth: ~190 KB of operand stages, less when the epilogue needs more staging / landing buffers
-  constexpr int STAGES = EPI == 1   ? ((BN == 256) ? 2 : (BN == 128 ? 4 : 5))
+  constexpr int STAGES = EPI == 1   ? ((BN == 256) ? 2 : (BN == 128 ? 3 : 4))
                          : EPI >= 2 ? ((BN == 256) ? 3 : (BN == 128 ? 5 : 6))
-                                    : ((BN == 256) ? 4 : (BN == 128 ? 6 : 8));
+                                    : ((BN == 256) ? (EW == 8 ? 3 : 4) : (BN == 128 ? 6 : 8));
   constexpr int kStageBytes = kStageABytes + BN * 128;
-  constexpr int smem = STAGES * kStageBytes + (2 * EW + (EPI == 1 ? 16 : 0)) * 4096 + (2 * STAGES + 20) * 8 + 16 + 1024;
+  constexpr int smem = STAGES * kStageBytes + (EPI == 1 ? 4 * EW : 2 * EW) * 4096 + (2 * STAGES + 36) * 8 + 16 + 1024;
   static_assert(smem <= 232448, "shared memory budget exceeded");
   auto kern = gemm_kernel<OP, DT, BN, STAGES, EPI, EW>;
   static bool configured[64] = {};
@@ -114,7 +116,16 @@ static int launch_bn(const GemmKParams& p, int bn, int grid, cudaStream_t stream
   switch (bn) {
     case 64: return launch_one<OP, DT, 64, EPI>(p, grid, stream);
     case 128: return launch_one<OP, DT, 128, EPI>(p, grid, stream);
-    default: return launch_one<OP, DT, 256, EPI>(p, grid, stream);
+    default:
+      if constexpr (EPI == 3 && DT == DDP_BF16)
+        if (p.dbg & 128) return launch_one<OP, DT, 256, EPI, 8>(p, grid, stream);
+      // Shallow-K score slabs (K = head dim) are bound by the epilogue, not the MMA: give them 8 epilogue
+      // warps (at the price of one smem stage, irrelevant when a tile has one or two k-blocks).
+      // (8 epilogue warps were tried for the plain shallow-K score slab as well: the TMEM drain gets faster,
+      //  0.144 vs 0.167 ms, but the slab write gets slower, 0.48 vs 0.42 ms; dbg bit 256 selects it.)
+      if constexpr (OP == DDP_OP_NT && EPI == 0)
+        if (p.k_blocks <= 2 && (p.dbg & 256)) return launch_one<OP, DT, 256, EPI, 8>(p, grid, stream);
+      return launch_one<OP, DT, 256, EPI>(p, grid, stream);
   }
 }
 
@@ -199,10 +210,17 @@ extern "C" int ddp_gemm_workspace(int op, const ddp_tensor* A, const ddp_tensor*
   return 0;
 }
 
+extern "C" int ddp_debug_timeout_site(void) {
+  unsigned int v = 0, zero = 0;
+  if (cudaMemcpyFromSymbol(&v, ddp::g_ddp_timeout_site, sizeof v) != cudaSuccess) return -1;
+  if (v) cudaMemcpyToSymbol(ddp::g_ddp_timeout_site, &zero, sizeof zero);
+  return static_cast<int>(v);
+}
+
 extern "C" int ddp_gemm_stats_tiles(const ddp_tensor* A, const ddp_tensor* B, int world) {
   Shapes s;
   if (derive_shapes(DDP_OP_NT, A, B, world, 1 << 30, &s)) return -1;
-  return world * s.n_blocks * 2;  // the statistics pass splits every tile into two column halves
+  return world * s.n_blocks * (s.bn >= 128 ? 2 : 1);  // tiles of >= 128 columns are split into two halves
 }
 
 extern "C" int ddp_gemm(int op, const ddp_tensor* A, const ddp_tensor* B, const ddp_tensor* C, float alpha,
@@ -342,7 +360,7 @@ extern "C" int ddp_gemm_ex(int op, const ddp_tensor* A, const ddp_tensor* B, con
     p.mb_sb1 = epi->mask_sb1_words;
     p.stats = reinterpret_cast<float2*>(epi->stats);
     p.rowstat = reinterpret_cast<const float2*>(epi->rowstat);
-    p.stats_nt = world * s.n_blocks * 2;  // two column halves per tile (8 epilogue warps)
+    p.stats_nt = world * s.n_blocks * (s.bn >= 128 ? 2 : 1);  // two column halves per tile with 8 epilogue warps
     p.epi_scale = epi->scale * 1.4426950408889634f;  // scores in the log2 domain
   }
   if (world > 1) {

@@ -131,6 +131,18 @@ __device__ __forceinline__ __half cvt_out<__half>(float v) {
   return __float2half_rn(v);
 }
 
+// Two fp32 values -> one packed 32-bit register of 16-bit floats (single F2FP, no stack traffic).
+template <typename T>
+__device__ __forceinline__ uint32_t pack2(float a, float b) {
+  if constexpr (std::is_same<T, __half>::value) {
+    const __half2 t = __floats2half2_rn(a, b);
+    return *reinterpret_cast<const uint32_t*>(&t);
+  } else {
+    const __nv_bfloat162 t = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<const uint32_t*>(&t);
+  }
+}
+
 // Epilogue staging tile of one warp: 32 rows x 128 bytes; 16-byte vector j of row r lives at slot
 // j ^ (r & 7) - exactly TMA's SWIZZLE_128B, so the same tile can leave through a TMA store or through
 // coalesced generic stores.  NF = 128 / sizeof(StoreT) values per row.
@@ -148,10 +160,12 @@ __device__ __forceinline__ void stage_row32(uint32_t sbuf, int row, const float 
   } else {
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-      StoreT h[8];
-#pragma unroll
-      for (int e = 0; e < 8; ++e) h[e] = cvt_out<StoreT>(v[8 * j + e]);
-      st_shared_v4(sbuf + row * 128 + (((part * 4 + j) ^ sw) * 16), *reinterpret_cast<uint4*>(h));
+      uint4 q;
+      q.x = pack2<StoreT>(v[8 * j + 0], v[8 * j + 1]);
+      q.y = pack2<StoreT>(v[8 * j + 2], v[8 * j + 3]);
+      q.z = pack2<StoreT>(v[8 * j + 4], v[8 * j + 5]);
+      q.w = pack2<StoreT>(v[8 * j + 6], v[8 * j + 7]);
+      st_shared_v4(sbuf + row * 128 + (((part * 4 + j) ^ sw) * 16), q);
     }
   }
 }
@@ -172,10 +186,18 @@ __device__ __forceinline__ void store_rows_generic(uint32_t sbuf, StoreT* dst, l
         if ((j + 1) * VE <= cols_valid) {
           st_v4(g, q);
         } else {
-          const StoreT* e = reinterpret_cast<const StoreT*>(&q);
+          const uint32_t w[4] = {q.x, q.y, q.z, q.w};
 #pragma unroll
-          for (int x = 0; x < VE; ++x)
-            if (j * VE + x < cols_valid) g[x] = e[x];
+          for (int x = 0; x < VE; ++x) {
+            if (j * VE + x < cols_valid) {
+              if constexpr (sizeof(StoreT) == 2) {
+                const unsigned short hbits = static_cast<unsigned short>(w[x / 2] >> (16 * (x & 1)));
+                g[x] = *reinterpret_cast<const StoreT*>(&hbits);
+              } else {
+                g[x] = *reinterpret_cast<const StoreT*>(&w[x]);
+              }
+            }
+          }
         }
       }
     }
@@ -184,7 +206,16 @@ __device__ __forceinline__ void store_rows_generic(uint32_t sbuf, StoreT* dst, l
       for (int c = lane; c < cols_valid; c += 32) {
         const int j = c / VE, x = c % VE;
         const uint4 q = ld_shared_v4(sbuf + r * 128 + ((j ^ (r & 7)) * 16));
-        dst[static_cast<long long>(r) * ld + c] = reinterpret_cast<const StoreT*>(&q)[x];
+        // select the element with shifts instead of indexing the register vector
+        constexpr int PER_WORD = 4 / sizeof(StoreT);
+        const int wi = x / PER_WORD;
+        uint32_t word = (wi & 2) ? ((wi & 1) ? q.w : q.z) : ((wi & 1) ? q.y : q.x);
+        if constexpr (sizeof(StoreT) == 2) {
+          const unsigned short hbits = static_cast<unsigned short>(word >> (16 * (x & 1)));
+          dst[static_cast<long long>(r) * ld + c] = *reinterpret_cast<const StoreT*>(&hbits);
+        } else {
+          dst[static_cast<long long>(r) * ld + c] = *reinterpret_cast<const StoreT*>(&word);
+        }
       }
     }
   }
@@ -193,7 +224,8 @@ __device__ __forceinline__ void store_rows_generic(uint32_t sbuf, StoreT* dst, l
 template <int OP, int DT, int BN, int STAGES, int EPI = 0, int EW = 4>
 __global__ void __launch_bounds__(kThreadsBase + 32 * EW, 1) gemm_kernel(const __grid_constant__ GemmKParams p) {
   static_assert(EW == 4 || EW == 8, "4 or 8 epilogue warps");
-  static_assert(EW == 4 || (OP == DDP_OP_NT && EPI != 1), "8 epilogue warps: nt without P prefetch only");
+  static_assert(EW == 4 || OP == DDP_OP_NT, "8 epilogue warps: nt only");
+  static_assert(EW == 4 || BN >= 128, "8 epilogue warps need two 128-byte chunks per row and tile");
   using InT = typename std::conditional<DT == DDP_F32, float,
                                         typename std::conditional<DT == DDP_BF16, __nv_bfloat16, __half>::type>::type;
   constexpr int ELEM = (DT == DDP_F32) ? 4 : 2;
@@ -211,15 +243,17 @@ __global__ void __launch_bounds__(kThreadsBase + 32 * EW, 1) gemm_kernel(const _
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* smem_ab = smem;                                   // STAGES x (A | B)
   char* smem_stage = reinterpret_cast<char*>(smem + STAGES * kStageBytes);  // EW warps x 2 x 4 KB
-  constexpr int kPBufs = 4;                   // EPI == 1: landing buffers per warp = TMA prefetch depth for P
-  char* smem_pst = smem_stage + 2 * EW * 4096;    // EPI == 1: 4 warps x kPBufs x 4 KB
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_stage + (EPI == 1 ? 2 * EW + 4 * kPBufs : 2 * EW) * 4096);
+  // EPI == 1: instead of staging buffers every warp owns a ring of kPBufs 4 KB buffers: P lands there by TMA
+  // (two chunks ahead), is turned into dS in place, and leaves from the same buffer by TMA store.
+  constexpr int kPBufs = 4;
+  char* smem_pst = smem_stage;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_stage + (EPI == 1 ? EW * kPBufs : 2 * EW) * 4096);
   uint64_t* full_bar = bars;                 // [STAGES]
   uint64_t* empty_bar = bars + STAGES;       // [STAGES]
   uint64_t* tfull_bar = bars + 2 * STAGES;   // [2]
   uint64_t* tempty_bar = tfull_bar + 2;      // [2]
-  uint64_t* p_bar = tempty_bar + 2;          // [4 warps][kPBufs]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(p_bar + 4 * kPBufs);
+  uint64_t* p_bar = tempty_bar + 2;          // [EW warps][kPBufs]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(p_bar + 8 * kPBufs);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -251,7 +285,7 @@ __global__ void __launch_bounds__(kThreadsBase + 32 * EW, 1) gemm_kernel(const _
       mbar_init(&tfull_bar[s], 1);
       mbar_init(&tempty_bar[s], EW);
     }
-    for (int s = 0; s < 4 * kPBufs; ++s) mbar_init(&p_bar[s], 1);
+    for (int s = 0; s < 8 * kPBufs; ++s) mbar_init(&p_bar[s], 1);
     fence_mbar_init();
   }
   if (warp == 2) tmem_alloc(tmem_slot, kTmemCols);
@@ -301,7 +335,7 @@ __global__ void __launch_bounds__(kThreadsBase + 32 * EW, 1) gemm_kernel(const _
               fence_proxy_async();
             }
           }
-          mbar_wait(&empty_bar[stage], phase ^ 1);
+          mbar_wait(&empty_bar[stage], phase ^ 1, 1);
           uint8_t* sa = smem_ab + stage * kStageBytes;
           uint8_t* sb = sa + kStageABytes;
           mbar_arrive_expect_tx(&full_bar[stage], kStageBytes);
@@ -349,11 +383,11 @@ __global__ void __launch_bounds__(kThreadsBase + 32 * EW, 1) gemm_kernel(const _
       const uint32_t mn_lbo = swap ? kMnGroup : static_cast<uint32_t>(BK * 128);
       const uint32_t mn_sbo = swap ? static_cast<uint32_t>(BK * 128) : kMnGroup;
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-        mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
+        mbar_wait(&tempty_bar[acc], acc_phase ^ 1, 2);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * BN;
         for (int it = 0; it < k_iters; ++it) {
-          mbar_wait(&full_bar[stage], phase);
+          mbar_wait(&full_bar[stage], phase, 3);
           tc_fence_after();
           const uint32_t sa = smem_u32(smem_ab + stage * kStageBytes);
           const uint32_t sb = sa + kStageABytes;
@@ -454,12 +488,14 @@ __global__ void __launch_bounds__(kThreadsBase + 32 * EW, 1) gemm_kernel(const _
       if (tt >= total_tiles) return;
       const TileCoord c2 = decode_tile<OP, BN, (EPI >= 2)>(p, tt);
       const int col = c2.seg * p.N + c2.n0 + ch * CW + ci * CCp;
-      uint64_t* bar = &p_bar[q * kPBufs + (gi % kPBufs)];
+      uint64_t* bar = &p_bar[ew * kPBufs + (gi % kPBufs)];
       mbar_arrive_expect_tx(bar, 4096);
       tma_load_5d(pbuf0 + (gi % kPBufs) * 4096, &p.tmP, bar, col, 0, c2.m0 + q * 32, c2.b0i, c2.b1i);
     };
-    if (EPI == 1 && lane == 0)
-      for (int i = 0; i < kPBufs - 1; ++i) issue_p(i);
+    if (EPI == 1 && lane == 0) {
+      issue_p(0);
+      issue_p(1);
+    }
     int acc = 0;
     uint32_t acc_phase = 0;
     uint32_t done_ok = 0;  // bitmask of peers whose done counter we have already checked (TN)
@@ -496,7 +532,7 @@ __global__ void __launch_bounds__(kThreadsBase + 32 * EW, 1) gemm_kernel(const _
         }
         if (EPI == 3 && row_ok) rstat = p.rowstat[static_cast<size_t>(tc.b) * p.M + row0 + lane];
       }
-      mbar_wait(&tfull_bar[acc], acc_phase);
+      mbar_wait(&tfull_bar[acc], acc_phase, 4);
       tc_fence_after();
       const bool tn_remote = (OP == DDP_OP_TN) && dist;
       if (tn_remote && tc.seg != p.rank && !(done_ok & (1u << tc.seg))) {
@@ -565,11 +601,16 @@ __global__ void __launch_bounds__(kThreadsBase + 32 * EW, 1) gemm_kernel(const _
           const int col0 = n0 + c0;
           const int cols_valid = min(CC, p.N - col0);
           const bool active = cols_valid > 0 && rows_valid > 0;  // warp-uniform
-          const char* pbuf = pbuf0 + (g % kPBufs) * 4096;
+          const uint32_t pbuf = smem_u32(pbuf0) + (g % kPBufs) * 4096;  // EPI 1: landing = staging buffer
           if constexpr (EPI == 1) {
             if (!to_peer) {
-              if (lane == 0) issue_p(g + kPBufs - 1);              // its buffer was drained one chunk ago
-              mbar_wait(&p_bar[q * kPBufs + (g % kPBufs)], (g / kPBufs) & 1);  // every chunk is loaded, used or not
+              if (lane == 0) {
+                // buffer (g+2) % kPBufs was last read by the TMA store of chunk g-2: all but the newest
+                // store group must have finished reading before P for chunk g+2 may land there
+                bulk_wait_group_read<1>();
+                issue_p(g + 2);
+              }
+              mbar_wait(&p_bar[ew * kPBufs + (g % kPBufs)], (g / kPBufs) & 1, 5);  // every chunk is loaded, used or not
               ++g;
             }
           }
@@ -592,8 +633,11 @@ __global__ void __launch_bounds__(kThreadsBase + 32 * EW, 1) gemm_kernel(const _
             for (int i = 0; i < NLD; ++i) tmem_ld_pin(r[i]);
           }
           if (p.dbg & 4) continue;  // harness only: time the TMEM drain alone
-          const uint32_t sbuf = smem_u32(sbuf0) + sb * 4096;  // shared-space address of this chunk's buffer
-          if (lane == 0) bulk_wait_group_read<1>();  // the TMA store that last read this buffer is done
+          // shared-space address of this chunk's staging buffer (EPI 1: the P landing buffer itself)
+          const uint32_t sbuf = (EPI == 1 && !to_peer) ? pbuf : smem_u32(sbuf0) + sb * 4096;
+          if (!(EPI == 1 && !to_peer)) {
+            if (lane == 0) bulk_wait_group_read<1>();  // the TMA store that last read this buffer is done
+          }
           __syncwarp();
           // 32 columns at a time: registers -> epilogue math -> this row's slice of the staging tile
 #pragma unroll
@@ -606,10 +650,6 @@ __global__ void __launch_bounds__(kThreadsBase + 32 * EW, 1) gemm_kernel(const _
             float v[32];
 #pragma unroll
             for (int e = 0; e < 32; ++e) v[e] = __uint_as_float(r[i][e]) * p.alpha;
-            if (p.dbg & 64) {  // harness: marker values instead of the accumulator (tests the store path alone)
-#pragma unroll
-              for (int e = 0; e < 32; ++e) v[e] = static_cast<float>(c0 + i * 32 + e);
-            }
             if (EPI == 3 && !(p.dbg & 32)) {  // dbg 32 (harness): store the raw scores instead
               // P = exp2(scale*log2e*s - (row max + log2 row sum)); masked entries are exactly 0 and a fully
               // masked row (rstat.x = NaN) is NaN, as softmax over a row of -inf is in the reference
@@ -635,7 +675,7 @@ __global__ void __launch_bounds__(kThreadsBase + 32 * EW, 1) gemm_kernel(const _
                 for (int j = 0; j < 4; ++j) {
                   const int jj = i * 4 + j;
                   const uint32_t slot = lane * 128 + ((jj ^ (lane & 7)) * 16);
-                  const uint4 pv = ld_shared_v4(smem_u32(pbuf) + slot);
+                  const uint4 pv = ld_shared_v4(pbuf + slot);
                   const P2* pp = reinterpret_cast<const P2*>(&pv);
                   uint4 ov;
                   P2* op = reinterpret_cast<P2*>(&ov);
@@ -664,7 +704,7 @@ __global__ void __launch_bounds__(kThreadsBase + 32 * EW, 1) gemm_kernel(const _
 #pragma unroll
                 for (int j = 0; j < VPP; ++j) {
                   const int jj = i * VPP + j;
-                  const uint4 pv = ld_shared_v4(smem_u32(pbuf) + lane * 128 + ((jj ^ (lane & 7)) * 16));
+                  const uint4 pv = ld_shared_v4(pbuf + lane * 128 + ((jj ^ (lane & 7)) * 16));
                   const StoreT* pe = reinterpret_cast<const StoreT*>(&pv);
 #pragma unroll
                   for (int e = 0; e < VE; ++e)

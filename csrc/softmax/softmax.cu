@@ -66,6 +66,13 @@ __device__ __forceinline__ float block_reduce(float v, float* red) {
 
 constexpr float kLog2e = 1.4426950408889634f;
 
+// 2^x on the SFU without the range fix-up code of exp2f (ex2(-inf) = 0, ex2(NaN) = NaN).
+__device__ __forceinline__ float ex2_fast(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 // ------------------------------------------------------------------ forward, register resident
 template <typename T> struct Packed2 { using type = __nv_bfloat162; };
 template <> struct Packed2<__half> { using type = __half2; };
@@ -110,15 +117,18 @@ __global__ void __launch_bounds__(THREADS, MINB) softmax_fwd_reg(const SmParams 
         if (v < nvec) {
           T* e = reinterpret_cast<T*>(&q[i]);
           if (mrow) {
-            uint8_t mb[VE];
+            // VE mask bytes in one load; the common all-clear case costs a single compare
+            unsigned long long mw;
             if constexpr (VE == 8) {
-              *reinterpret_cast<uint2*>(mb) = *reinterpret_cast<const uint2*>(mrow + static_cast<long long>(v) * VE);
+              mw = *reinterpret_cast<const unsigned long long*>(mrow + static_cast<long long>(v) * VE);
             } else {
-              *reinterpret_cast<uint32_t*>(mb) = *reinterpret_cast<const uint32_t*>(mrow + static_cast<long long>(v) * VE);
+              mw = *reinterpret_cast<const uint32_t*>(mrow + static_cast<long long>(v) * VE);
             }
+            if (mw != 0ull) {
 #pragma unroll
-            for (int k = 0; k < VE; ++k)
-              if (mb[k]) e[k] = from_f<T>(-INFINITY);
+              for (int k = 0; k < VE; ++k)
+                if ((mw >> (8 * k)) & 0xffull) e[k] = from_f<T>(-INFINITY);
+            }
           }
           mx = vec_max<T>(q[i], mx);  // max of raw scores; scale > 0 commutes with max
         }
@@ -133,7 +143,8 @@ __global__ void __launch_bounds__(THREADS, MINB) softmax_fwd_reg(const SmParams 
           T* e = reinterpret_cast<T*>(&q[i]);
 #pragma unroll
           for (int k = 0; k < VE; ++k) {
-            const float ex = exp2f(to_f(e[k]) * s2 - m2);  // fully masked row: -inf - -inf = NaN, as the reference
+            // one FFMA + one MUFU.EX2; fully masked row: -inf - -inf = NaN, as the reference
+            const float ex = ex2_fast(fmaf(to_f(e[k]), s2, -m2));
             sum += ex;
             e[k] = from_f<T>(ex);
           }
