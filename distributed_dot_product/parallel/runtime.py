@@ -221,11 +221,18 @@ def check_status():
     status word of the symmetric heap and carries on with invalid data.  Call this (it synchronises the
     device) at step boundaries of long jobs, or after an unexpected result, to turn that into an exception.
     """
+    if not torch.cuda.is_available() or not _native.available():
+        return 0
+    lib = _native.load()
+    torch.cuda.synchronize()
+    site = lib.ddp_debug_timeout_site()
+    if site > 0:
+        raise RuntimeError('distributed-dot-product: an in-kernel pipeline wait gave up after 4 s (site %d: '
+                           '1 smem slot, 2 TMEM buffer, 3 operands, 4 accumulator, 5 P chunk); results are '
+                           'invalid - please report this shape' % site)
     hp = _Heap._instance
     if hp is None or hp.base is None:
         return 0
-    torch.cuda.synchronize()
-    lib = _native.load()
     host = ctypes.c_uint32(0)
     rc = lib.ddp_read_u32(ctypes.c_void_p(hp.base + 384), ctypes.byref(host))
     _native.check(rc)
