@@ -12,7 +12,7 @@ ours() { port=$((port+1)); timeout 300 $RUN --master-port $port benchmarks/bench
 ref()  { port=$((port+1)); timeout 300 $RUN --master-port $port baseline/bench_ops_reference.py "$@" 2>/dev/null | grep '^{' >> "$OUT"; }
 # config 2: nt sweep, d = 768, fp32 (tf32), fwd+bwd
 TS="1024 4096 8192 16384 24576"; DS="2 16 64 256 768"
-if [ "$MODE" = reduced ]; then TS="24576"; DS="64 768"; fi
+if [ "$MODE" = reduced ]; then TS="24576"; DS="768"; fi
 for T in $TS; do
   ours --mode nt --length $T --dim 768 --dtype fp32 --backward --offset 1024
   ref  --mode nt --length $T --dim 768 --backward --offset 1024

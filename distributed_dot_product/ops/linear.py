@@ -30,6 +30,23 @@ def colsum(x2):
     return out
 
 
+def _weight_grad(g2, x2):
+    """``dW = dy^T x`` on the TN kernel.  A tall-skinny problem (many rows, few output tiles) would leave most
+    SMs idle, so the row (= K) dimension is split into S batches that run as one batched TN launch and the S
+    partial products are summed afterwards (split-K)."""
+    rows, n_out, n_in = g2.size(0), g2.size(1), x2.size(1)
+    tiles = ((n_out + 127) // 128) * ((n_in + 255) // 256)
+    split = 1
+    if g2.is_contiguous() and x2.is_contiguous():
+        while split < 8 and tiles * split * 2 <= 148 and rows % (split * 2 * 64) == 0 and rows // (split * 2) >= 1024:
+            split *= 2
+    if split == 1:
+        return _g.gemm(_native.OP_TN, g2, x2, distributed=False)
+    part = _g.gemm(_native.OP_TN, g2.view(split, rows // split, n_out), x2.view(split, rows // split, n_in),
+                   distributed=False)
+    return part.float().sum(0).to(g2.dtype)
+
+
 class _Linear(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, weight, bias):
@@ -48,7 +65,7 @@ class _Linear(torch.autograd.Function):
         if ctx.needs_input_grad[0]:
             gx = _g.gemm(_native.OP_NN, g2, weight, distributed=False).reshape(x.shape)
         if ctx.needs_input_grad[1]:
-            gw = _g.gemm(_native.OP_TN, g2, x2, distributed=False)
+            gw = _weight_grad(g2, x2)
         if ctx.has_bias and ctx.needs_input_grad[2]:
             g2c = g2 if g2.stride(-1) == 1 else g2.contiguous()
             gb = colsum(g2c)
