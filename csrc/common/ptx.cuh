@@ -58,7 +58,7 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
   return ok != 0;
 }
 // Last pipeline wait that gave up (0 = none): see mbar_wait.  Read and cleared by ddp_debug_timeout_site().
-__device__ unsigned int g_ddp_timeout_site = 0;
+static __device__ unsigned int g_ddp_timeout_site = 0;
 
 // Spins on an mbarrier phase.  A pipeline bug must not hang the GPU (and whoever shares it): after ~4 s of
 // spinning the wait gives up, records which wait it was (`site`) and returns; the kernel then finishes with
@@ -94,6 +94,13 @@ __device__ __forceinline__ void tma_load_5d(void* smem_dst, const CUtensorMap* m
       ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1),
       "r"(c2), "r"(c3), "r"(c4)
       : "memory");
+}
+// 1-D bulk copy global -> shared (TMA engine, no tensor map), completion on an mbarrier (bytes).
+// dst, src and bytes must be multiples of 16.
+__device__ __forceinline__ void bulk_load_1d(uint32_t smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(smem_dst), "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
 }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async;" ::: "memory"); }
 // Generic-proxy writes to shared memory -> visible to the async proxy (before a TMA store reads them).

@@ -15,6 +15,7 @@
 
 #include "../../include/ddp_b200.h"
 #include "../common/host_util.h"
+#include "../common/ptx.cuh"
 
 namespace ddp {
 
@@ -161,6 +162,117 @@ __global__ void __launch_bounds__(THREADS, MINB) softmax_fwd_reg(const SmParams 
           for (int k = 0; k < VE; ++k) e[k] = from_f<T>(to_f(e[k]) * inv);
           *reinterpret_cast<uint4*>(yr + static_cast<long long>(v) * VE) = q[i];
         }
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------ forward, long rows (software pipelined)
+// Rows of 32-128 KB need most of the register file of an SM, so only one CTA fits and the register-resident
+// kernel above alternates "load the row" and "compute the row" with nothing to overlap them.  Here the NEXT
+// row streams into shared memory through the TMA engine (cp.async.bulk, mbarrier completion) while the
+// current one is being reduced, exponentiated and written: per row the SM pays max(load, compute + store)
+// instead of their sum.
+template <typename T, int VPT>
+__global__ void __launch_bounds__(512, 1) softmax_fwd_pipe(const SmParams p) {
+  constexpr int VE = 16 / sizeof(T);
+  constexpr int THREADS = 512;
+  extern __shared__ __align__(128) uint8_t sm_raw[];
+  __shared__ float red[32];
+  __shared__ __align__(8) uint64_t bar;
+  const uint32_t row_smem = smem_u32(sm_raw);
+  const int nvec = p.cols / VE;
+  const uint32_t row_bytes = static_cast<uint32_t>(p.cols) * sizeof(T);
+  const int items = p.b1 * p.rows;
+  const float s2 = p.scale * kLog2e;
+  // this CTA's rows, in order: item = blockIdx.x + k * gridDim.x, heads innermost (mask row reuse)
+  const int my_items = (items - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
+  const long long my_rows = static_cast<long long>(blockIdx.x < static_cast<unsigned>(items) ? my_items : 0) * p.b0;
+  auto row_ptr = [&](long long r, const void* base, long long ld, long long sb0, long long sb1) {
+    const int it = static_cast<int>(r / p.b0), h = static_cast<int>(r - static_cast<long long>(it) * p.b0);
+    const int item = blockIdx.x + it * gridDim.x;
+    const int b1i = item / p.rows, row = item - b1i * p.rows;
+    return reinterpret_cast<const T*>(base) + b1i * sb1 + h * sb0 + static_cast<long long>(row) * ld;
+  };
+  auto issue_row = [&](long long r) {  // one thread
+    const T* src = row_ptr(r, p.x, p.x_ld, p.x_sb0, p.x_sb1);
+    mbar_arrive_expect_tx(&bar, row_bytes);
+    for (uint32_t off = 0; off < row_bytes; off += 32768u) {
+      const uint32_t n = row_bytes - off < 32768u ? row_bytes - off : 32768u;
+      bulk_load_1d(row_smem + off, reinterpret_cast<const uint8_t*>(src) + off, n, &bar);
+    }
+  };
+  if (threadIdx.x == 0) {
+    mbar_init(&bar, 1);
+    fence_mbar_init();
+  }
+  __syncthreads();
+  if (threadIdx.x == 0 && my_rows > 0) issue_row(0);
+  uint32_t phase = 0;
+  for (long long r = 0; r < my_rows; ++r) {
+    const int it = static_cast<int>(r / p.b0);
+    const int item = blockIdx.x + it * gridDim.x;
+    const int b1i = item / p.rows, row = item - b1i * p.rows;
+    const uint8_t* mrow = p.mask ? p.mask + b1i * p.m_sb1 + static_cast<long long>(row) * p.m_ld : nullptr;
+    T* yr = const_cast<T*>(row_ptr(r, p.out, p.o_ld, p.o_sb0, p.o_sb1));
+    mbar_wait(&bar, phase, 6);
+    phase ^= 1;
+    uint4 q[VPT];
+#pragma unroll
+    for (int i = 0; i < VPT; ++i) {
+      const int v = threadIdx.x + i * THREADS;
+      if (v < nvec) q[i] = ld_shared_v4(row_smem + static_cast<uint32_t>(v) * 16u);
+    }
+    __syncthreads();  // the whole row is in registers: the buffer may take the next row
+    if (threadIdx.x == 0 && r + 1 < my_rows) issue_row(r + 1);
+    float mx = -INFINITY;
+#pragma unroll
+    for (int i = 0; i < VPT; ++i) {
+      const int v = threadIdx.x + i * THREADS;
+      if (v < nvec) {
+        T* e = reinterpret_cast<T*>(&q[i]);
+        if (mrow) {
+          unsigned long long mw;
+          if constexpr (VE == 8) {
+            mw = *reinterpret_cast<const unsigned long long*>(mrow + static_cast<long long>(v) * VE);
+          } else {
+            mw = *reinterpret_cast<const uint32_t*>(mrow + static_cast<long long>(v) * VE);
+          }
+          if (mw != 0ull) {
+#pragma unroll
+            for (int k = 0; k < VE; ++k)
+              if ((mw >> (8 * k)) & 0xffull) e[k] = from_f<T>(-INFINITY);
+          }
+        }
+        mx = vec_max<T>(q[i], mx);
+      }
+    }
+    mx = block_reduce<true>(mx, red) * p.scale;
+    const float m2 = mx * kLog2e;
+    float sum = 0.f;
+#pragma unroll
+    for (int i = 0; i < VPT; ++i) {
+      const int v = threadIdx.x + i * THREADS;
+      if (v < nvec) {
+        T* e = reinterpret_cast<T*>(&q[i]);
+#pragma unroll
+        for (int k = 0; k < VE; ++k) {
+          const float ex = ex2_fast(fmaf(to_f(e[k]), s2, -m2));
+          sum += ex;
+          e[k] = from_f<T>(ex);
+        }
+      }
+    }
+    sum = block_reduce<false>(sum, red);
+    const float inv = 1.f / sum;
+#pragma unroll
+    for (int i = 0; i < VPT; ++i) {
+      const int v = threadIdx.x + i * THREADS;
+      if (v < nvec) {
+        T* e = reinterpret_cast<T*>(&q[i]);
+#pragma unroll
+        for (int k = 0; k < VE; ++k) e[k] = from_f<T>(to_f(e[k]) * inv);
+        *reinterpret_cast<uint4*>(yr + static_cast<long long>(v) * VE) = q[i];
       }
     }
   }
@@ -336,10 +448,27 @@ static int launch_fwd(const SmParams& p, bool vec_ok, cudaStream_t st) {
       softmax_fwd_reg<T, 8, 128, 6><<<min(items, sms * 6), 128, 0, st>>>(p);
     } else if (nvec <= 2048) {
       softmax_fwd_reg<T, 8, 256, 3><<<min(items, sms * 3), 256, 0, st>>>(p);
-    } else if (nvec <= 4096) {
-      softmax_fwd_reg<T, 8, 512, 1><<<min(items, sms * 2), 512, 0, st>>>(p);
     } else {
-      softmax_fwd_reg<T, 16, 512, 1><<<min(items, sms), 512, 0, st>>>(p);
+      // long rows: next row streams into shared memory (TMA bulk copy) while the current one is processed
+      const int smem = p.cols * static_cast<int>(sizeof(T));
+      static bool configured[2][64] = {};
+      int dev = 0;
+      cudaGetDevice(&dev);
+      if (nvec <= 4096) {
+        auto kern = softmax_fwd_pipe<T, 8>;
+        if (dev < 64 && !configured[0][dev]) {
+          cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536);
+          configured[0][dev] = true;
+        }
+        kern<<<min(items, sms), 512, smem, st>>>(p);
+      } else {
+        auto kern = softmax_fwd_pipe<T, 16>;
+        if (dev < 64 && !configured[1][dev]) {
+          cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 131072);
+          configured[1][dev] = true;
+        }
+        kern<<<min(items, sms), 512, smem, st>>>(p);
+      }
     }
   } else {
     softmax_fwd_stream<T><<<min(items, sms * 4), p.cols >= 4096 ? 512 : 256, 0, st>>>(p);
@@ -514,4 +643,11 @@ extern "C" int ddp_softmax_combine(const void* stats, int64_t n_rows, int32_t nt
   ddp::softmax_combine_kernel<<<static_cast<unsigned>(blocks), threads, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const float2*>(stats), n_rows, nt, static_cast<float2*>(rowstat));
   return ddp::cuda_check(cudaGetLastError(), "softmax_combine launch");
+}
+
+extern "C" int ddp_debug_timeout_site_rowops(void) {
+  unsigned int v = 0, zero = 0;
+  if (cudaMemcpyFromSymbol(&v, ddp::g_ddp_timeout_site, sizeof v) != cudaSuccess) return -1;
+  if (v) cudaMemcpyToSymbol(ddp::g_ddp_timeout_site, &zero, sizeof zero);
+  return static_cast<int>(v);
 }

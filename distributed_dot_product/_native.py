@@ -93,6 +93,7 @@ def load():
         lib.ddp_heap_close.argtypes = [c.c_void_p]
         lib.ddp_heap_free.argtypes = [c.c_void_p]
         lib.ddp_debug_timeout_site.restype = c.c_int
+        lib.ddp_debug_timeout_site_rowops.restype = c.c_int
         lib.ddp_read_u32.argtypes = [c.c_void_p, c.POINTER(c.c_uint32)]
         lib.ddp_memset_async.argtypes = [c.c_void_p, c.c_int, c.c_size_t, c.c_void_p]
         _lib = lib

@@ -91,12 +91,19 @@ def _stream():
     return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
-def chunk_rows_from_offset(offset, rows):
-    """Staging granularity of the in-kernel all-gather: ``offset`` rows per published chunk, rounded
-    up to the 64-row swizzle atom (reference semantics of ``offset``: functions.py:64-68)."""
+def chunk_rows_from_offset(offset, rows, batch=1):
+    """Staging granularity of the in-kernel all-gather: ``offset`` rows per published chunk (reference
+    semantics of ``offset``: functions.py:64-68), rounded up to 64 rows - but never so coarse that the push
+    runs on a handful of warps: one warp pushes one (batch, chunk) item, so small problems get finer chunks
+    (down to 16 rows) until there are about two items per SM."""
     offset = max(int(offset), 1)
     c = (offset + 63) // 64 * 64
-    return max(64, min(c, (rows + 63) // 64 * 64))
+    c = max(64, min(c, (rows + 63) // 64 * 64))
+    want_items = 2 * 148
+    if batch * ((rows + c - 1) // c) < want_items:
+        fine = (rows * batch) // want_items // 16 * 16
+        c = min(c, max(16, fine))
+    return c
 
 
 def _unsqueeze4(t):
@@ -176,7 +183,7 @@ def gemm(op, left, right, offset=32, out=None, alpha=1.0, bias=None, distributed
     va, vb, vc = as_view(a), as_view(b), as_view(c4)
     comm_ptr = None
     if world > 1:
-        chunk = chunk_rows_from_offset(offset, rows_r)
+        chunk = chunk_rows_from_offset(offset, rows_r, a.size(0) * a.size(1))
         ws = ctypes.c_size_t()
         nf = ctypes.c_size_t()
         _native.check(lib.ddp_gemm_workspace(op, ctypes.byref(va), ctypes.byref(vb), world, chunk,

@@ -97,6 +97,7 @@ typedef struct ddp_epilogue {
 /* Pipeline watchdog: id of the last in-kernel mbarrier wait that gave up after 4 s (0 = none; 1 smem slot free,
  * 2 TMEM buffer free, 3 operands landed, 4 accumulator ready, 5 P chunk landed); synchronises, clears the id. */
 int ddp_debug_timeout_site(void);
+int ddp_debug_timeout_site_rowops(void); /* same, for the softmax kernels (site 6 = row landed) */
 int ddp_gemm_stats_tiles(const ddp_tensor* A, const ddp_tensor* B, int world);
 /* bits[b1][rows][ld_words] <- mask u8 [b1][rows][cols] (nonzero = masked); bits past `cols` are set. */
 int ddp_pack_mask(const uint8_t* mask, int64_t b1, int64_t rows, int64_t cols, int64_t mask_ld, int64_t mask_sb1,

@@ -87,7 +87,7 @@ def test_products_unaligned_and_strided_views(cuda_device):
 
 
 @pytest.mark.parametrize('dtype', [torch.bfloat16, torch.float32])
-@pytest.mark.parametrize('cols', [64, 1000, 5000, 40000])
+@pytest.mark.parametrize('cols', [64, 1000, 5000, 20000, 40000])
 def test_masked_softmax_fwd_bwd(cuda_device, dtype, cols):
     from distributed_dot_product.ops.softmax import masked_softmax, masked_softmax_
     torch.manual_seed(2)
