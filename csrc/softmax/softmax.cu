@@ -11,6 +11,7 @@
 #include <cuda_runtime.h>
 
 #include <cfloat>
+#include <cstdlib>
 #include <cstdint>
 
 #include "../../include/ddp_b200.h"
@@ -92,6 +93,31 @@ __device__ __forceinline__ float vec_max(const uint4& q, float mx) {
   }
 }
 
+// Mask bits of this thread's VPT vectors (bit j*VE+k = element k of vector j), built once per (batch, row) and
+// reused for every head: the mask loads leave the per-row critical path (they were its main stall).
+template <int VPT, int VE, int THREADS>
+__device__ __forceinline__ void load_mask_bits(const uint8_t* mrow, int nvec, uint32_t (&bits)[(VPT * VE + 31) / 32]) {
+#pragma unroll
+  for (int w = 0; w < (VPT * VE + 31) / 32; ++w) bits[w] = 0u;
+  if (mrow == nullptr) return;
+#pragma unroll
+  for (int i = 0; i < VPT; ++i) {
+    const int v = threadIdx.x + i * THREADS;
+    if (v < nvec) {
+      unsigned long long mw;
+      if constexpr (VE == 8) {
+        mw = *reinterpret_cast<const unsigned long long*>(mrow + static_cast<long long>(v) * VE);
+      } else {
+        mw = *reinterpret_cast<const uint32_t*>(mrow + static_cast<long long>(v) * VE);
+      }
+      uint32_t b = 0;
+#pragma unroll
+      for (int k = 0; k < VE; ++k) b |= ((mw >> (8 * k)) & 0xffull) ? (1u << k) : 0u;
+      bits[(i * VE) / 32] |= b << ((i * VE) % 32);
+    }
+  }
+}
+
 template <typename T, int VPT, int THREADS, int MINB>
 __global__ void __launch_bounds__(THREADS, MINB) softmax_fwd_reg(const SmParams p) {
   constexpr int VE = 16 / sizeof(T);
@@ -102,6 +128,8 @@ __global__ void __launch_bounds__(THREADS, MINB) softmax_fwd_reg(const SmParams 
   for (int item = blockIdx.x; item < items; item += gridDim.x) {
     const int b1i = item / p.rows, row = item - b1i * p.rows;
     const uint8_t* mrow = p.mask ? p.mask + b1i * p.m_sb1 + static_cast<long long>(row) * p.m_ld : nullptr;
+    uint32_t mbits[(VPT * VE + 31) / 32];
+    load_mask_bits<VPT, VE, THREADS>(mrow, nvec, mbits);
     for (int h = 0; h < p.b0; ++h) {
       const T* xr = reinterpret_cast<const T*>(p.x) + b1i * p.x_sb1 + h * p.x_sb0 + static_cast<long long>(row) * p.x_ld;
       T* yr = reinterpret_cast<T*>(p.out) + b1i * p.o_sb1 + h * p.o_sb0 + static_cast<long long>(row) * p.o_ld;
@@ -117,19 +145,11 @@ __global__ void __launch_bounds__(THREADS, MINB) softmax_fwd_reg(const SmParams 
         const int v = threadIdx.x + i * THREADS;
         if (v < nvec) {
           T* e = reinterpret_cast<T*>(&q[i]);
-          if (mrow) {
-            // VE mask bytes in one load; the common all-clear case costs a single compare
-            unsigned long long mw;
-            if constexpr (VE == 8) {
-              mw = *reinterpret_cast<const unsigned long long*>(mrow + static_cast<long long>(v) * VE);
-            } else {
-              mw = *reinterpret_cast<const uint32_t*>(mrow + static_cast<long long>(v) * VE);
-            }
-            if (mw != 0ull) {
+          const uint32_t mb = (mbits[(i * VE) / 32] >> ((i * VE) % 32)) & ((1u << VE) - 1u);
+          if (mb != 0u) {
 #pragma unroll
-              for (int k = 0; k < VE; ++k)
-                if ((mw >> (8 * k)) & 0xffull) e[k] = from_f<T>(-INFINITY);
-            }
+            for (int k = 0; k < VE; ++k)
+              if ((mb >> k) & 1u) e[k] = from_f<T>(-INFINITY);
           }
           mx = vec_max<T>(q[i], mx);  // max of raw scores; scale > 0 commutes with max
         }
@@ -173,10 +193,9 @@ __global__ void __launch_bounds__(THREADS, MINB) softmax_fwd_reg(const SmParams 
 // row streams into shared memory through the TMA engine (cp.async.bulk, mbarrier completion) while the
 // current one is being reduced, exponentiated and written: per row the SM pays max(load, compute + store)
 // instead of their sum.
-template <typename T, int VPT>
-__global__ void __launch_bounds__(512, 1) softmax_fwd_pipe(const SmParams p) {
+template <typename T, int VPT, int THREADS, int MINB>
+__global__ void __launch_bounds__(THREADS, MINB) softmax_fwd_pipe(const SmParams p) {
   constexpr int VE = 16 / sizeof(T);
-  constexpr int THREADS = 512;
   extern __shared__ __align__(128) uint8_t sm_raw[];
   __shared__ float red[32];
   __shared__ __align__(8) uint64_t bar;
@@ -209,11 +228,15 @@ __global__ void __launch_bounds__(512, 1) softmax_fwd_pipe(const SmParams p) {
   __syncthreads();
   if (threadIdx.x == 0 && my_rows > 0) issue_row(0);
   uint32_t phase = 0;
+  uint32_t mbits[(VPT * VE + 31) / 32];
   for (long long r = 0; r < my_rows; ++r) {
     const int it = static_cast<int>(r / p.b0);
     const int item = blockIdx.x + it * gridDim.x;
     const int b1i = item / p.rows, row = item - b1i * p.rows;
-    const uint8_t* mrow = p.mask ? p.mask + b1i * p.m_sb1 + static_cast<long long>(row) * p.m_ld : nullptr;
+    if (r % p.b0 == 0) {  // new (batch, row): its mask bits serve all heads
+      const uint8_t* mrow = p.mask ? p.mask + b1i * p.m_sb1 + static_cast<long long>(row) * p.m_ld : nullptr;
+      load_mask_bits<VPT, VE, THREADS>(mrow, nvec, mbits);
+    }
     T* yr = const_cast<T*>(row_ptr(r, p.out, p.o_ld, p.o_sb0, p.o_sb1));
     mbar_wait(&bar, phase, 6);
     phase ^= 1;
@@ -231,18 +254,11 @@ __global__ void __launch_bounds__(512, 1) softmax_fwd_pipe(const SmParams p) {
       const int v = threadIdx.x + i * THREADS;
       if (v < nvec) {
         T* e = reinterpret_cast<T*>(&q[i]);
-        if (mrow) {
-          unsigned long long mw;
-          if constexpr (VE == 8) {
-            mw = *reinterpret_cast<const unsigned long long*>(mrow + static_cast<long long>(v) * VE);
-          } else {
-            mw = *reinterpret_cast<const uint32_t*>(mrow + static_cast<long long>(v) * VE);
-          }
-          if (mw != 0ull) {
+        const uint32_t mb = (mbits[(i * VE) / 32] >> ((i * VE) % 32)) & ((1u << VE) - 1u);
+        if (mb != 0u) {
 #pragma unroll
-            for (int k = 0; k < VE; ++k)
-              if ((mw >> (8 * k)) & 0xffull) e[k] = from_f<T>(-INFINITY);
-          }
+          for (int k = 0; k < VE; ++k)
+            if ((mb >> k) & 1u) e[k] = from_f<T>(-INFINITY);
         }
         mx = vec_max<T>(q[i], mx);
       }
@@ -276,6 +292,141 @@ __global__ void __launch_bounds__(512, 1) softmax_fwd_pipe(const SmParams p) {
       }
     }
   }
+}
+
+// ------------------------------------------------------------------ forward, long rows split over a cluster
+// A 64-128 KB row fills the register file of an SM, so at most one row per SM is in flight and its phases
+// (load, max, exp, sum, scale, store) run back to back; the exp phase alone is SFU-bound (8 ex2/clk/SM).
+// Splitting every row over a thread-block cluster of CS CTAs of 128 threads puts 4 independent row slices on
+// each SM, whose phases overlap; the two row-wide reductions go through distributed shared memory.
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ float ld_dsmem_f32(const float* local_ptr, uint32_t cta) {
+  uint32_t raddr;
+  float v;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(raddr) : "r"(smem_u32(local_ptr)), "r"(cta));
+  asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(raddr) : "memory");
+  return v;
+}
+
+template <typename T, int CS>
+__global__ void __launch_bounds__(128, 4) softmax_fwd_cluster(const SmParams p) {
+  constexpr int VE = 16 / sizeof(T);
+  constexpr int THREADS = 128;
+  constexpr int VPT = 16;
+  __shared__ float red[32];
+  __shared__ float part[2][2];  // [row parity][0 = max, 1 = sum] of this CTA's slice
+  const uint32_t crank = cluster_ctarank();
+  const int cluster_id = blockIdx.x / CS;
+  const int n_clusters = gridDim.x / CS;
+  const int nvec = p.cols / VE;
+  const int nvec_cta = nvec / CS;          // host guarantees nvec % CS == 0 and nvec_cta <= THREADS * VPT
+  const int v0 = crank * nvec_cta;
+  const int items = p.b1 * p.rows;
+  const float s2 = p.scale * kLog2e;
+  int parity = 0;
+  for (int item = cluster_id; item < items; item += n_clusters) {
+    const int b1i = item / p.rows, row = item - b1i * p.rows;
+    const uint8_t* mrow = p.mask ? p.mask + b1i * p.m_sb1 + static_cast<long long>(row) * p.m_ld : nullptr;
+    for (int h = 0; h < p.b0; ++h, parity ^= 1) {
+      const T* xr = reinterpret_cast<const T*>(p.x) + b1i * p.x_sb1 + h * p.x_sb0 + static_cast<long long>(row) * p.x_ld;
+      T* yr = reinterpret_cast<T*>(p.out) + b1i * p.o_sb1 + h * p.o_sb0 + static_cast<long long>(row) * p.o_ld;
+      uint4 q[VPT];
+#pragma unroll
+      for (int i = 0; i < VPT; ++i) {
+        const int v = threadIdx.x + i * THREADS;
+        if (v < nvec_cta) q[i] = *reinterpret_cast<const uint4*>(xr + static_cast<long long>(v0 + v) * VE);
+      }
+      float mx = -INFINITY;
+#pragma unroll
+      for (int i = 0; i < VPT; ++i) {
+        const int v = threadIdx.x + i * THREADS;
+        if (v < nvec_cta) {
+          T* e = reinterpret_cast<T*>(&q[i]);
+          if (mrow) {
+            unsigned long long mw;
+            if constexpr (VE == 8) {
+              mw = *reinterpret_cast<const unsigned long long*>(mrow + static_cast<long long>(v0 + v) * VE);
+            } else {
+              mw = *reinterpret_cast<const uint32_t*>(mrow + static_cast<long long>(v0 + v) * VE);
+            }
+            if (mw != 0ull) {
+#pragma unroll
+              for (int k = 0; k < VE; ++k)
+                if ((mw >> (8 * k)) & 0xffull) e[k] = from_f<T>(-INFINITY);
+            }
+          }
+          mx = vec_max<T>(q[i], mx);
+        }
+      }
+      mx = block_reduce<true>(mx, red);
+      if (threadIdx.x == 0) part[parity][0] = mx;
+      cluster_sync_all();
+      float gmx = -INFINITY;
+#pragma unroll
+      for (int c = 0; c < CS; ++c) gmx = fmaxf(gmx, ld_dsmem_f32(&part[parity][0], c));
+      const float m2 = gmx * p.scale * kLog2e;
+      float sum = 0.f;
+#pragma unroll
+      for (int i = 0; i < VPT; ++i) {
+        const int v = threadIdx.x + i * THREADS;
+        if (v < nvec_cta) {
+          T* e = reinterpret_cast<T*>(&q[i]);
+#pragma unroll
+          for (int k = 0; k < VE; ++k) {
+            const float ex = ex2_fast(fmaf(to_f(e[k]), s2, -m2));
+            sum += ex;
+            e[k] = from_f<T>(ex);
+          }
+        }
+      }
+      sum = block_reduce<false>(sum, red);
+      if (threadIdx.x == 0) part[parity][1] = sum;
+      cluster_sync_all();
+      float gsum = 0.f;
+#pragma unroll
+      for (int c = 0; c < CS; ++c) gsum += ld_dsmem_f32(&part[parity][1], c);
+      const float inv = 1.f / gsum;
+#pragma unroll
+      for (int i = 0; i < VPT; ++i) {
+        const int v = threadIdx.x + i * THREADS;
+        if (v < nvec_cta) {
+          T* e = reinterpret_cast<T*>(&q[i]);
+#pragma unroll
+          for (int k = 0; k < VE; ++k) e[k] = from_f<T>(to_f(e[k]) * inv);
+          *reinterpret_cast<uint4*>(yr + static_cast<long long>(v0 + v) * VE) = q[i];
+        }
+      }
+    }
+  }
+  cluster_sync_all();  // no CTA may exit while a peer can still read its shared memory
+}
+
+template <typename T, int CS>
+static int launch_fwd_cluster(const SmParams& p, int items, int sms, cudaStream_t st) {
+  int clusters = (sms * 4) / CS;
+  if (clusters > items) clusters = items;
+  if (clusters < 1) clusters = 1;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(static_cast<unsigned>(clusters * CS));
+  cfg.blockDim = dim3(128);
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = CS;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cuda_check(cudaLaunchKernelEx(&cfg, softmax_fwd_cluster<T, CS>, p), "softmax_fwd_cluster launch");
 }
 
 // ------------------------------------------------------------------ forward, streaming (any shape)
@@ -448,6 +599,10 @@ static int launch_fwd(const SmParams& p, bool vec_ok, cudaStream_t st) {
       softmax_fwd_reg<T, 8, 128, 6><<<min(items, sms * 6), 128, 0, st>>>(p);
     } else if (nvec <= 2048) {
       softmax_fwd_reg<T, 8, 256, 3><<<min(items, sms * 3), 256, 0, st>>>(p);
+    } else if (nvec % 2 == 0 && nvec / 2 <= 2048 && getenv("DDP_SOFTMAX_CLUSTER")) {  // experimental, slower
+      return launch_fwd_cluster<T, 2>(p, items, sms, st);   // rows of 32-64 KB: 2 CTAs per row
+    } else if (nvec % 4 == 0 && nvec / 4 <= 2048 && getenv("DDP_SOFTMAX_CLUSTER")) {
+      return launch_fwd_cluster<T, 4>(p, items, sms, st);   // rows of 64-128 KB: 4 CTAs per row
     } else {
       // long rows: next row streams into shared memory (TMA bulk copy) while the current one is processed
       const int smem = p.cols * static_cast<int>(sizeof(T));
@@ -455,14 +610,15 @@ static int launch_fwd(const SmParams& p, bool vec_ok, cudaStream_t st) {
       int dev = 0;
       cudaGetDevice(&dev);
       if (nvec <= 4096) {
-        auto kern = softmax_fwd_pipe<T, 8>;
+        // rows up to 64 KB: 256 threads x 16 vectors, two CTAs (= two rows in different phases) per SM
+        auto kern = softmax_fwd_pipe<T, 16, 256, 2>;
         if (dev < 64 && !configured[0][dev]) {
           cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536);
           configured[0][dev] = true;
         }
-        kern<<<min(items, sms), 512, smem, st>>>(p);
+        kern<<<min(items, sms * 2), 256, smem, st>>>(p);
       } else {
-        auto kern = softmax_fwd_pipe<T, 16>;
+        auto kern = softmax_fwd_pipe<T, 16, 512, 1>;
         if (dev < 64 && !configured[1][dev]) {
           cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 131072);
           configured[1][dev] = true;
