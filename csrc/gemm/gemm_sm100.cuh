@@ -296,23 +296,27 @@ __global__ void __launch_bounds__(kThreadsBase + 32 * EW, 1) gemm_kernel(const _
 
   if (warp == 0) {
     // ======================================================= TMA producer
-    if (lane == 0) {
+    // The whole warp walks the tile / k-block sequence (uniform control flow): all 32 lanes poll the peer
+    // flags a tile or rank segment depends on in parallel (one round trip instead of one per flag), lane 0
+    // alone talks to the mbarriers and issues the TMA loads.
+    {
       int stage = 0;
       uint32_t phase = 0;
       const uint32_t* my_flags = p.flags[p.rank];
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
         const TileCoord tc = decode_tile<OP, BN, (EPI >= 2)>(p, t);
         const int n0 = tc.n0;
+        bool need_fence = false;
         if (OP == DDP_OP_NT && dist && tc.seg != p.rank) {
           // gathered rows [n0, n0+BN) of rank seg must have landed in our buffer
           const int c_lo = n0 / p.chunk_rows;
-          const int hi_row = min(n0 + BN, p.N) - 1;
-          const int c_hi = hi_row / p.chunk_rows;
-          for (int c = c_lo; c <= c_hi; ++c)
-            wait_flag_ge(my_flags + (static_cast<size_t>(tc.seg) * Bt + tc.b) * p.n_chunks + c, p.seq, p.status, 1);
-          fence_proxy_async();
+          const int c_hi = (min(n0 + BN, p.N) - 1) / p.chunk_rows;
+          const uint32_t* f = my_flags + (static_cast<size_t>(tc.seg) * Bt + tc.b) * p.n_chunks;
+          for (int c = c_lo + lane; c <= c_hi; c += 32) wait_flag_ge(f + c, p.seq, p.status, 1);
+          __syncwarp();
+          need_fence = true;
         }
-        int waited_seg = -1, waited_chunk = -1;
+        int polled_seg = -1;
         for (int it = 0; it < k_iters; ++it) {
           int seg = tc.seg, kb = it;
           if (OP == DDP_OP_NN) {
@@ -321,46 +325,44 @@ __global__ void __launch_bounds__(kThreadsBase + 32 * EW, 1) gemm_kernel(const _
             seg = (p.rank + si) % p.world;
           }
           const int k0 = kb * BK;
-          if (OP == DDP_OP_NN && dist && seg != p.rank) {
-            const int c_lo = k0 / p.chunk_rows;
-            const int c_hi = (min(k0 + BK, p.K) - 1) / p.chunk_rows;
-            if (seg != waited_seg) {
-              waited_seg = seg;
-              waited_chunk = -1;
-            }
-            if (c_hi > waited_chunk) {
-              for (int c = max(c_lo, waited_chunk + 1); c <= c_hi; ++c)
-                wait_flag_ge(my_flags + (static_cast<size_t>(seg) * Bt + tc.b) * p.n_chunks + c, p.seq, p.status, 2);
-              waited_chunk = c_hi;
-              fence_proxy_async();
-            }
+          if (OP == DDP_OP_NN && dist && seg != p.rank && seg != polled_seg) {
+            // first k-block of a remote rank segment: all of its chunks for this batch, lane-parallel
+            const uint32_t* f = my_flags + (static_cast<size_t>(seg) * Bt + tc.b) * p.n_chunks;
+            for (int c = lane; c < p.n_chunks; c += 32) wait_flag_ge(f + c, p.seq, p.status, 2);
+            __syncwarp();
+            polled_seg = seg;
+            need_fence = true;
           }
-          mbar_wait(&empty_bar[stage], phase ^ 1, 1);
-          uint8_t* sa = smem_ab + stage * kStageBytes;
-          uint8_t* sb = sa + kStageABytes;
-          mbar_arrive_expect_tx(&full_bar[stage], kStageBytes);
-          // ---- A
-          if constexpr (!A_MN) {
-            tma_load_5d(sa, &p.tmA, &full_bar[stage], k0 + seg * p.a_seg_c0, seg * p.a_seg_c1, tc.m0, tc.b0i,
-                        tc.b1i);
-          } else {
+          if (lane == 0) {
+            if (need_fence) fence_proxy_async();  // peer (generic-proxy) writes -> our TMA (async-proxy) reads
+            mbar_wait(&empty_bar[stage], phase ^ 1, 1);
+            uint8_t* sa = smem_ab + stage * kStageBytes;
+            uint8_t* sb = sa + kStageABytes;
+            mbar_arrive_expect_tx(&full_bar[stage], kStageBytes);
+            // ---- A
+            if constexpr (!A_MN) {
+              tma_load_5d(sa, &p.tmA, &full_bar[stage], k0 + seg * p.a_seg_c0, seg * p.a_seg_c1, tc.m0, tc.b0i,
+                          tc.b1i);
+            } else {
 #pragma unroll
-            for (int j = 0; j < kBlockM / CH; ++j)
-              tma_load_5d(sa + j * (BK * 128), &p.tmA, &full_bar[stage], tc.seg * p.M + tc.m0 + j * CH, 0, k0,
-                          tc.b0i, tc.b1i);
-          }
-          // ---- B
-          const bool remote = (OP != DDP_OP_TN) && dist && seg != p.rank;
-          const CUtensorMap* mb = remote ? &p.tmBg : &p.tmB;
-          const int c3 = remote ? tc.b : tc.b0i;
-          const int c4 = remote ? seg : tc.b1i;
-          if constexpr (!B_MN) {
-            tma_load_5d(sb, mb, &full_bar[stage], k0, 0, n0, c3, c4);
-          } else {
+              for (int j = 0; j < kBlockM / CH; ++j)
+                tma_load_5d(sa + j * (BK * 128), &p.tmA, &full_bar[stage], tc.seg * p.M + tc.m0 + j * CH, 0, k0,
+                            tc.b0i, tc.b1i);
+            }
+            // ---- B
+            const bool remote = (OP != DDP_OP_TN) && dist && seg != p.rank;
+            const CUtensorMap* mb = remote ? &p.tmBg : &p.tmB;
+            const int c3 = remote ? tc.b : tc.b0i;
+            const int c4 = remote ? seg : tc.b1i;
+            if constexpr (!B_MN) {
+              tma_load_5d(sb, mb, &full_bar[stage], k0, 0, n0, c3, c4);
+            } else {
 #pragma unroll
-            for (int j = 0; j < BN / CH; ++j)
-              tma_load_5d(sb + j * (BK * 128), mb, &full_bar[stage], n0 + j * CH, 0, k0, c3, c4);
+              for (int j = 0; j < BN / CH; ++j)
+                tma_load_5d(sb + j * (BK * 128), mb, &full_bar[stage], n0 + j * CH, 0, k0, c3, c4);
+            }
           }
+          need_fence = false;
           if (++stage == STAGES) {
             stage = 0;
             phase ^= 1;
@@ -803,12 +805,37 @@ __global__ void __launch_bounds__(kThreadsBase + 32 * EW, 1) gemm_kernel(const _
         const int cols_valid = max(0, min(BN, p.N - col0));
         const float* part = reinterpret_cast<const float*>(p.ws[p.rank]);
         OutT* out = reinterpret_cast<OutT*>(p.C) + b1i * p.c_sb1 + b0i * p.c_sb0;
-        for (int rr = 0; rr < rows_valid; ++rr) {
-          for (int cc = lane; cc < cols_valid; cc += 32) {
-            float s = 0.f;
-            for (int src = 0; src < p.world; ++src)
-              s += part[((static_cast<size_t>(src) * Bt + b) * p.M + row0 + rr) * p.N + col0 + cc];
-            out[static_cast<long long>(row0 + rr) * p.ldc + col0 + cc] = cvt_out<OutT>(s);
+        const size_t src_stride = static_cast<size_t>(Bt) * p.M * p.N;  // floats between two sources' slots
+        const float* base = part + (static_cast<size_t>(b) * p.M + row0) * p.N + col0;
+        if ((p.N & 3) == 0) {
+          // float4 per lane; the loads of all sources are issued before the first add (fixed summation order)
+          const int c4n = cols_valid >> 2;
+          const int total = rows_valid * c4n;
+          for (int idx = lane; idx < total; idx += 32) {
+            const int rr = idx / c4n, c4 = idx - rr * c4n;
+            const float* src0 = base + static_cast<size_t>(rr) * p.N + c4 * 4;
+            float4 v[DDP_MAX_WORLD];
+#pragma unroll
+            for (int src = 0; src < DDP_MAX_WORLD; ++src)
+              if (src < p.world) v[src] = *reinterpret_cast<const float4*>(src0 + src * src_stride);
+            float4 acc4 = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+            for (int src = 0; src < DDP_MAX_WORLD; ++src)
+              if (src < p.world) {
+                acc4.x += v[src].x; acc4.y += v[src].y; acc4.z += v[src].z; acc4.w += v[src].w;
+              }
+            OutT* o = out + static_cast<long long>(row0 + rr) * p.ldc + col0 + c4 * 4;
+            o[0] = cvt_out<OutT>(acc4.x); o[1] = cvt_out<OutT>(acc4.y);
+            o[2] = cvt_out<OutT>(acc4.z); o[3] = cvt_out<OutT>(acc4.w);
+          }
+        } else {
+          for (int rr = 0; rr < rows_valid; ++rr) {
+            for (int cc = lane; cc < cols_valid; cc += 32) {
+              float s = 0.f;
+              for (int src = 0; src < p.world; ++src)
+                s += base[src * src_stride + static_cast<size_t>(rr) * p.N + cc];
+              out[static_cast<long long>(row0 + rr) * p.ldc + col0 + cc] = cvt_out<OutT>(s);
+            }
           }
         }
       }
