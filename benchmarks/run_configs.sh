@@ -4,12 +4,13 @@
 N=${1:-1}
 OUT=${2:-gpurun_out/configs_n$N.jsonl}
 MODE=${3:-full}   # "reduced" = the largest point of every sweep only (multi-GPU budget)
+ARMS=${4:-both}   # "ours" = skip the reference arm
 RUN="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1"
 mkdir -p "$(dirname "$OUT")"
 : > "$OUT"
 port=29700
 ours() { port=$((port+1)); timeout 300 $RUN --master-port $port benchmarks/benchmark.py --file /tmp/bench_$$.json --no-dense "$@" 2>/dev/null | grep '^{' >> "$OUT"; rm -f /tmp/bench_$$.json; }
-ref()  { port=$((port+1)); timeout 300 $RUN --master-port $port baseline/bench_ops_reference.py "$@" 2>/dev/null | grep '^{' >> "$OUT"; }
+ref()  { [ "$ARMS" = ours ] && return; port=$((port+1)); timeout 300 $RUN --master-port $port baseline/bench_ops_reference.py "$@" 2>/dev/null | grep '^{' >> "$OUT"; }
 # config 2: nt sweep, d = 768, fp32 (tf32), fwd+bwd
 TS="1024 4096 8192 16384 24576"; DS="2 16 64 256 768"
 if [ "$MODE" = reduced ]; then TS="24576"; DS="768"; fi
