@@ -22,12 +22,15 @@ LIB_SOURCES = [
     "csrc/gemm/gemm_api.cu",
     "csrc/softmax/softmax.cu",
     "csrc/reduce/colsum.cu",
+    "csrc/attn/attn_api.cu",
 ]
 HEADERS = [
     "include/ddp_b200.h",
     "csrc/common/ptx.cuh",
     "csrc/common/host_util.h",
     "csrc/gemm/gemm_sm100.cuh",
+    "csrc/gemm/tma_map.h",
+    "csrc/attn/attn_fwd_sm100.cuh",
 ]
 LIB_OUT = "distributed_dot_product/_lib/libddp_b200.so"
 
@@ -75,7 +78,7 @@ def build_harness():
     srcs = [s for s in LIB_SOURCES if os.path.exists(os.path.join(ROOT, s))]
     objs = [compile_obj(s) for s in srcs]
     os.makedirs(os.path.join(ROOT, "build"), exist_ok=True)
-    for name in ("gemm_harness",):
+    for name in ("gemm_harness", "attn_harness"):
         src = "csrc/tests/%s.cu" % name
         if not os.path.exists(os.path.join(ROOT, src)):
             continue

@@ -1,0 +1,514 @@
+// Slab-free attention forward for sm_100a with the all-gather fused in:
+//
+//     O[rows, :] = softmax(scale * A . gather(B)^T  masked) . gather(V)         (reference: module.py:61-69)
+//
+// A = this rank's rows (the reference's keys), B / V = the column-side operands of ALL ranks (the reference's
+// queries / values).  The [T/N x T] score slab never exists: scores live in TMEM, probabilities go through
+// shared memory straight back into the tensor core (online softmax), only O (and the row log-sum-exp) is
+// written.  One persistent CTA per SM, 384 threads:
+//
+//   warp 0      TMA producer: A tiles (two 128-row blocks per work item) and a ring of (B_j, V_j) column blocks;
+//               polls the peers' per-chunk flags before touching gathered rows
+//   warp 1      MMA issuer:   S_w = A_w . B_j^T (128x128, K = d) and O_w += P_w . V_j (128 x dv, K = 128) for the
+//               two row blocks w = 0, 1, interleaved so that one block's softmax overlaps the other's MMAs
+//   warps 2-3   TMEM alloc; all-gather pushers (B and V chunks -> every peer's workspace, one flag per chunk)
+//   warps 4-7   softmax warpgroup of row block 0 (thread = row): TMEM S -> max / exp2 / sum -> bf16 P in smem,
+//   warps 8-11  same for row block 1;  rescales the O accumulator in TMEM only when the running max moved by
+//               more than 2^8 (lazy rescale), normalises and stores O at the end of the row block.
+#pragma once
+#include "../gemm/gemm_sm100.cuh"
+
+namespace ddp {
+
+constexpr int kAtThreads = 384;
+constexpr int kAtBM = 128;                 // rows per warpgroup tile
+constexpr int kAtBN = 128;                 // columns per step
+constexpr int kAtTile = 128 * 128;         // 128 rows x 128 bytes
+constexpr int kAtPBytes = 2 * kAtTile;     // P tile of one warpgroup: two 64-column k-chunks
+constexpr int kAtStageBytes = 2 * kAtTile; // B_j | V_j
+constexpr uint32_t kAtTmemCols = 512;      // S0 S1 (128 each) | O0 O1 (64 each)
+constexpr float kAtTau = 8.f;              // lazy-rescale threshold (log2 units)
+
+struct alignas(64) AttnKParams {
+  CUtensorMap tmA;   // [b1][b0][M][d]     box 64 x 128 rows
+  CUtensorMap tmB;   // [b1][b0][Tn][d]    box 64 x 128 rows (K-major B operand of S)
+  CUtensorMap tmV;   // [b1][b0][Tn][dv]   box 64 x 128 rows (MN-major B operand of O)
+  CUtensorMap tmBg;  // gathered [world][Bt][Tn][d]
+  CUtensorMap tmVg;  // gathered [world][Bt][Tn][dv]
+  CUtensorMap tmO;   // [b1][b0][M][dv]    box 64 x 32 rows (TMA store)
+  int M, Tn, dv;
+  int b0, b1;
+  int world, rank;
+  int m_pairs;   // pairs of 128-row blocks per batch entry
+  int n_blocks;  // 128-column blocks per rank segment
+  void* O;
+  long long ldo, o_sb0, o_sb1;
+  int o_vec_ok, o_tma_ok;
+  float* lse;  // [Bt][M]: row max + log2(row sum), log2 domain; may be null
+  const uint32_t* mask_bits;
+  long long mb_ld, mb_sb1;
+  float scale_log2;  // scale * log2(e) > 0
+  // collective
+  uint32_t seq;
+  int phase_mask;
+  int chunk_rows, n_chunks;
+  char* ws[DDP_MAX_WORLD];
+  uint32_t* flags[DDP_MAX_WORLD];
+  uint32_t* done[DDP_MAX_WORLD];
+  uint32_t* exit_counter;
+  uint32_t* status;
+  long long ws_v_off;  // byte offset of the gathered V region inside a workspace
+  const char* push_src[2];
+  long long push_ld[2], push_sb0[2], push_sb1[2];
+  int push_rows, push_row_bytes[2];
+  int dbg;  // bit 0 (harness): P = scale_log2 * S without max / exp / normalisation (linear, isolates the MMAs)
+};
+
+template <int DT, int STAGES>
+__global__ void __launch_bounds__(kAtThreads, 1) attn_fwd_kernel(const __grid_constant__ AttnKParams p) {
+  using T = typename std::conditional<DT == DDP_BF16, __nv_bfloat16, __half>::type;
+  static_assert(DT == DDP_BF16 || DT == DDP_F16, "16-bit operands only");
+
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sA = smem;                       // 2 x 16 KB
+  uint8_t* sP = sA + 2 * kAtTile;           // 2 x 32 KB
+  uint8_t* sKV = sP + 2 * kAtPBytes;        // STAGES x 32 KB
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sKV + STAGES * kAtStageBytes);
+  uint64_t* kv_full = bars;                 // [STAGES]
+  uint64_t* kv_empty = bars + STAGES;       // [STAGES]
+  uint64_t* a_full = bars + 2 * STAGES;     // [1]
+  uint64_t* a_empty = a_full + 1;           // [1]
+  uint64_t* s_full = a_empty + 1;           // [2]  S_w landed in TMEM
+  uint64_t* s_empty = s_full + 2;           // [2]  warpgroup w has read S_w
+  uint64_t* p_full = s_empty + 2;           // [2]  P_w staged (and O_w rescaled)
+  uint64_t* o_done = p_full + 2;            // [2]  O_w += P_w V_j finished
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_done + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int Bt = p.b0 * p.b1;
+  const bool dist = p.world > 1;
+  const bool do_produce = (p.phase_mask & 1) != 0;
+  const bool do_consume = (p.phase_mask & 2) != 0;
+  const int items = do_consume ? p.b1 * p.m_pairs * p.b0 : 0;
+  const int nj = p.world * p.n_blocks;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&p.tmA);
+    tma_prefetch_desc(&p.tmB);
+    tma_prefetch_desc(&p.tmV);
+    if (dist) {
+      tma_prefetch_desc(&p.tmBg);
+      tma_prefetch_desc(&p.tmVg);
+    }
+    if (p.o_tma_ok) tma_prefetch_desc(&p.tmO);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&kv_full[s], 1);
+      mbar_init(&kv_empty[s], 1);
+    }
+    mbar_init(a_full, 1);
+    mbar_init(a_empty, 1);
+    for (int w = 0; w < 2; ++w) {
+      mbar_init(&s_full[w], 1);
+      mbar_init(&s_empty[w], 4);
+      mbar_init(&p_full[w], 4);
+      mbar_init(&o_done[w], 1);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 2) tmem_alloc(tmem_slot, kAtTmemCols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  // work item -> (outer batch, row-block pair, head); heads fastest so the CTAs that run at the same time share
+  // their mask rows in L2
+  auto decode = [&](int it, int& b1i, int& b0i, int& m0) {
+    b0i = it % p.b0;
+    const int r = it / p.b0;
+    const int pair = r % p.m_pairs;
+    b1i = r / p.m_pairs;
+    m0 = pair * (2 * kAtBM);
+  };
+
+  if (warp == 0) {
+    // ======================================================= TMA producer (whole warp walks the loop)
+    int stage = 0;
+    uint32_t ph = 0, a_ph = 0;
+    const uint32_t* my_flags = p.flags[p.rank];
+    for (int it = blockIdx.x; it < items; it += gridDim.x) {
+      int b1i, b0i, m0;
+      decode(it, b1i, b0i, m0);
+      const int b = b1i * p.b0 + b0i;
+      if (lane == 0) {
+        mbar_wait(a_empty, a_ph ^ 1, 11);
+        mbar_arrive_expect_tx(a_full, 2 * kAtTile);
+        tma_load_5d(sA, &p.tmA, a_full, 0, 0, m0, b0i, b1i);
+        tma_load_5d(sA + kAtTile, &p.tmA, a_full, 0, 0, m0 + kAtBM, b0i, b1i);
+      }
+      a_ph ^= 1;
+      for (int si = 0; si < p.world; ++si) {
+        const int seg = (p.rank + si) % p.world;
+        const bool remote = dist && seg != p.rank;
+        bool need_fence = false;
+        if (remote) {
+          // every chunk of both gathered operands of rank `seg` for this batch entry, lane-parallel
+          for (int c = lane; c < 2 * p.n_chunks; c += 32) {
+            const int which = c / p.n_chunks, cc = c - which * p.n_chunks;
+            const uint32_t* f =
+                my_flags + ((static_cast<size_t>(which) * p.world + seg) * Bt + b) * p.n_chunks + cc;
+            wait_flag_ge(f, p.seq, p.status, 6);
+          }
+          __syncwarp();
+          need_fence = true;
+        }
+        for (int nb = 0; nb < p.n_blocks; ++nb) {
+          if (lane == 0) {
+            if (need_fence) fence_proxy_async();  // peer (generic-proxy) writes -> our TMA (async-proxy) reads
+            mbar_wait(&kv_empty[stage], ph ^ 1, 12);
+            uint8_t* sb = sKV + stage * kAtStageBytes;
+            mbar_arrive_expect_tx(&kv_full[stage], kAtStageBytes);
+            const int n0 = nb * kAtBN;
+            if (remote) {
+              tma_load_5d(sb, &p.tmBg, &kv_full[stage], 0, 0, n0, b, seg);
+              tma_load_5d(sb + kAtTile, &p.tmVg, &kv_full[stage], 0, 0, n0, b, seg);
+            } else {
+              tma_load_5d(sb, &p.tmB, &kv_full[stage], 0, 0, n0, b0i, b1i);
+              tma_load_5d(sb + kAtTile, &p.tmV, &kv_full[stage], 0, 0, n0, b0i, b1i);
+            }
+          }
+          need_fence = false;
+          if (++stage == STAGES) {
+            stage = 0;
+            ph ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ======================================================= MMA issuer
+    if (lane == 0) {
+      constexpr uint32_t kIdS = umma_idesc(DT, 0u, 0u, kAtBM, kAtBN);  // A K-major, B K-major
+      constexpr uint32_t kIdO = umma_idesc(DT, 0u, 1u, kAtBM, 64);     // A = P K-major, B = V MN-major
+      int stage = 0;
+      uint32_t ph = 0, a_ph = 0;
+      uint32_t se_ph0 = 0, se_ph1 = 0, pf_ph0 = 0, pf_ph1 = 0;
+      const uint32_t sA_u = smem_u32(sA), sP_u = smem_u32(sP), sKV_u = smem_u32(sKV);
+      auto issue_S = [&](int w, uint32_t sb) {
+        uint32_t& se = w ? se_ph1 : se_ph0;
+        mbar_wait(&s_empty[w], se ^ 1, 13);
+        se ^= 1;
+        tc_fence_after();
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk)
+          umma_ss<false>(tmem_base + w * kAtBN, umma_smem_desc(sA_u + w * kAtTile + kk * 32, 16, 1024),
+                         umma_smem_desc(sb + kk * 32, 16, 1024), kIdS, kk != 0 ? 1u : 0u);
+        umma_commit(&s_full[w]);
+      };
+      for (int it = blockIdx.x; it < items; it += gridDim.x) {
+        mbar_wait(a_full, a_ph, 14);
+        a_ph ^= 1;
+        mbar_wait(&kv_full[stage], ph, 15);
+        tc_fence_after();
+        issue_S(0, sKV_u + stage * kAtStageBytes);
+        issue_S(1, sKV_u + stage * kAtStageBytes);
+        for (int j = 0; j < nj; ++j) {
+          const uint32_t sv = sKV_u + stage * kAtStageBytes + kAtTile;
+          const int nstage = (stage + 1 == STAGES) ? 0 : stage + 1;
+          const uint32_t nph = (nstage == 0) ? (ph ^ 1) : ph;
+#pragma unroll
+          for (int w = 0; w < 2; ++w) {
+            uint32_t& pf = w ? pf_ph1 : pf_ph0;
+            mbar_wait(&p_full[w], pf, 16);
+            pf ^= 1;
+            tc_fence_after();
+#pragma unroll
+            for (int kk = 0; kk < 8; ++kk)
+              umma_ss<false>(tmem_base + 2 * kAtBN + w * 64,
+                             umma_smem_desc(sP_u + w * kAtPBytes + (kk >> 2) * kAtTile + (kk & 3) * 32, 16, 1024),
+                             umma_smem_desc(sv + kk * 2048, kAtTile, 1024, 2), kIdO, (j | kk) != 0 ? 1u : 0u);
+            umma_commit(&o_done[w]);
+            if (j + 1 < nj) {
+              if (w == 0) {
+                mbar_wait(&kv_full[nstage], nph, 15);
+                tc_fence_after();
+              }
+              issue_S(w, sKV_u + nstage * kAtStageBytes);
+            }
+          }
+          umma_commit(&kv_empty[stage]);
+          stage = nstage;
+          ph = nph;
+        }
+        umma_commit(a_empty);
+      }
+    }
+  } else if (warp < 4) {
+    // ======================================================= all-gather pushers (B and V)
+    if (dist && do_produce) {
+      const int gw = blockIdx.x * 2 + (warp - 2);
+      const int gstride = gridDim.x * 2;
+      const int per_which = Bt * p.n_chunks;
+      const int n_items = 2 * per_which;
+      if (gw < n_items) {
+        // The peers must have finished call seq-2 before we overwrite this parity of their workspace.
+        if (lane > 0 && lane < p.world) {
+          const int q = (p.rank + lane) % p.world;
+          wait_flag_ge(p.done[p.rank] + q, p.seq - 2u, p.status, 3);
+        }
+        __syncwarp();
+      }
+      for (int item = gw; item < n_items; item += gstride) {
+        const int which = item / per_which;
+        const int rem = item - which * per_which;
+        const int b = rem / p.n_chunks;
+        const int c = rem - b * p.n_chunks;
+        const int b1i = b / p.b0, b0i = b - b1i * p.b0;
+        const int r0 = c * p.chunk_rows;
+        const int nrows = min(p.chunk_rows, p.push_rows - r0);
+        const int rb = p.push_row_bytes[which];
+        const int vpr = rb / 16;
+        const long long ld = p.push_ld[which];
+        const char* src = p.push_src[which] + b1i * p.push_sb1[which] + b0i * p.push_sb0[which] +
+                          static_cast<long long>(r0) * ld;
+        const size_t dst_off = (which ? static_cast<size_t>(p.ws_v_off) : 0) +
+                               ((static_cast<size_t>(p.rank) * Bt + b) * p.push_rows + r0) * static_cast<size_t>(rb);
+        const int nvec = nrows * vpr;
+        for (int v0 = 0; v0 < nvec; v0 += 32 * 4) {
+          uint4 qv[4];
+          int rr[4], jj[4];
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const int v = v0 + u * 32 + lane;
+            rr[u] = v / vpr;
+            jj[u] = v - rr[u] * vpr;
+            if (v < nvec) qv[u] = ld_nc_v4(src + static_cast<long long>(rr[u]) * ld + jj[u] * 16);
+          }
+          for (int i = 1; i < p.world; ++i) {
+            const int peer = (p.rank - i + p.world) % p.world;  // rank-1 consumes our rows first
+            char* dst = p.ws[peer] + dst_off;
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const int v = v0 + u * 32 + lane;
+              if (v < nvec) st_v4(dst + static_cast<size_t>(rr[u]) * rb + jj[u] * 16, qv[u]);
+            }
+          }
+        }
+        __threadfence_system();
+        __syncwarp();
+        if (lane > 0 && lane < p.world) {
+          const int peer = (p.rank - lane + p.world) % p.world;
+          st_release_sys(p.flags[peer] + ((static_cast<size_t>(which) * p.world + p.rank) * Bt + b) * p.n_chunks + c,
+                         p.seq);
+        }
+        __syncwarp();
+      }
+    }
+  } else {
+    // ======================================================= softmax warpgroups (thread = row)
+    const int w = (warp - 4) >> 2;  // row block of the pair
+    const int q = warp & 3;         // TMEM lane quadrant this warp may access (= warp id mod 4)
+    const int row_in = q * 32 + lane;
+    const uint32_t tS = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + w * kAtBN;
+    const uint32_t tO = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + 2 * kAtBN + w * 64;
+    const uint32_t sPw = smem_u32(sP) + w * kAtPBytes;
+    const uint32_t sw = lane & 7;
+    const bool raw = (p.dbg & 1) != 0;
+    uint32_t sf_ph = 0, od_ph = 0;
+    for (int it = blockIdx.x; it < items; it += gridDim.x) {
+      int b1i, b0i, m0;
+      decode(it, b1i, b0i, m0);
+      const int b = b1i * p.b0 + b0i;
+      const int row0 = m0 + w * kAtBM + q * 32;  // first row of this warp
+      const int row = row0 + lane;
+      const uint32_t* mrow = nullptr;
+      if (p.mask_bits != nullptr)
+        mrow = p.mask_bits + b1i * p.mb_sb1 + static_cast<long long>(min(row, p.M - 1)) * p.mb_ld;
+      float m_used = -INFINITY, l = 0.f;
+      int j = 0;
+      for (int si = 0; si < p.world; ++si) {
+        const int seg = (p.rank + si) % p.world;
+        for (int nb = 0; nb < p.n_blocks; ++nb, ++j) {
+          const int n0 = nb * kAtBN;
+          const int nvalid = min(kAtBN, p.Tn - n0);
+          // mask words of this row for the 128 columns of the step (bit set = masked out), fetched before the
+          // wait so that their latency hides behind the MMA
+          uint32_t mk[4] = {0u, 0u, 0u, 0u};
+          if (mrow != nullptr) {
+            const uint32_t* mp = mrow + ((static_cast<long long>(seg) * p.Tn + n0) >> 5);
+            const int nw = (nvalid + 31) >> 5;
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+              if (i < nw) mk[i] = __ldg(mp + i);
+          }
+          if (nvalid < kAtBN) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const int lo = i * 32;
+              if (nvalid <= lo) {
+                mk[i] = 0xffffffffu;
+              } else if (nvalid < lo + 32) {
+                mk[i] |= 0xffffffffu << (nvalid - lo);
+              }
+            }
+          }
+          mbar_wait(&s_full[w], sf_ph, 17);
+          sf_ph ^= 1;
+          tc_fence_after();
+          // ---- pass A: row maximum of the raw scores over the live columns
+          float mx = -INFINITY;
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            uint32_t r[32];
+            tmem_ld_32x32(tS + c * 32, r);
+            tmem_ld_wait();
+            tmem_ld_pin(r);
+            if (mk[c] == 0u) {
+#pragma unroll
+              for (int e = 0; e < 32; ++e) mx = fmaxf(mx, __uint_as_float(r[e]));
+            } else {
+#pragma unroll
+              for (int e = 0; e < 32; ++e)
+                if (!((mk[c] >> e) & 1u)) mx = fmaxf(mx, __uint_as_float(r[e]));
+            }
+          }
+          const float m_blk = mx * p.scale_log2;  // scale_log2 > 0; -inf stays -inf
+          // Lazy rescale: the reference point of the exponentials only moves when the maximum grew by more than
+          // 2^kAtTau, so P stays <= 2^kAtTau and the O accumulator is rarely touched.
+          const bool need = !raw && (m_blk > m_used + kAtTau);
+          if (j > 0) {
+            // O_w += P_w V_{j-1} has finished: P_w may be overwritten, O_w may be rescaled
+            mbar_wait(&o_done[w], od_ph, 18);
+            od_ph ^= 1;
+            tc_fence_after();
+            if (__any_sync(0xffffffffu, need)) {
+              const float f = need ? ex2_approx(m_used - m_blk) : 1.f;
+#pragma unroll
+              for (int h = 0; h < 2; ++h) {
+                uint32_t r[32];
+                tmem_ld_32x32(tO + h * 32, r);
+                tmem_ld_wait();
+                tmem_ld_pin(r);
+#pragma unroll
+                for (int e = 0; e < 32; ++e) r[e] = __float_as_uint(__uint_as_float(r[e]) * f);
+                tmem_st_32x32(tO + h * 32, r);
+              }
+              tmem_st_wait();
+              l *= f;
+            }
+          }
+          if (need) m_used = m_blk;
+          const float neg_m = (raw || m_used == -INFINITY) ? 0.f : -m_used;
+          // ---- pass B: P = exp2(scale_log2 * S - m) -> bf16 tile in shared memory (K-major, 128B swizzle)
+          float l0 = 0.f, l1 = 0.f, l2 = 0.f, l3 = 0.f;
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            uint32_t r[32];
+            tmem_ld_32x32(tS + c * 32, r);
+            tmem_ld_wait();
+            tmem_ld_pin(r);
+            float v[32];
+            if (raw) {
+#pragma unroll
+              for (int e = 0; e < 32; ++e)
+                v[e] = ((mk[c] >> e) & 1u) ? 0.f : __uint_as_float(r[e]) * p.scale_log2;
+            } else if (mk[c] == 0u) {
+#pragma unroll
+              for (int e = 0; e < 32; ++e) v[e] = ex2_approx(fmaf(__uint_as_float(r[e]), p.scale_log2, neg_m));
+            } else {
+#pragma unroll
+              for (int e = 0; e < 32; ++e)
+                v[e] = ((mk[c] >> e) & 1u) ? 0.f : ex2_approx(fmaf(__uint_as_float(r[e]), p.scale_log2, neg_m));
+            }
+#pragma unroll
+            for (int e = 0; e < 32; e += 4) {
+              l0 += v[e];
+              l1 += v[e + 1];
+              l2 += v[e + 2];
+              l3 += v[e + 3];
+            }
+            const uint32_t base = sPw + (c >> 1) * kAtTile + row_in * 128;
+#pragma unroll
+            for (int jv = 0; jv < 4; ++jv) {
+              uint4 qv;
+              qv.x = pack2<T>(v[8 * jv + 0], v[8 * jv + 1]);
+              qv.y = pack2<T>(v[8 * jv + 2], v[8 * jv + 3]);
+              qv.z = pack2<T>(v[8 * jv + 4], v[8 * jv + 5]);
+              qv.w = pack2<T>(v[8 * jv + 6], v[8 * jv + 7]);
+              st_shared_v4(base + ((((c & 1) * 4 + jv) ^ sw) * 16), qv);
+            }
+          }
+          l += (l0 + l1) + (l2 + l3);
+          tc_fence_before();           // our TMEM reads (S) and writes (O) precede the MMAs released below
+          fence_proxy_async_smem();    // P (generic-proxy stores) -> tensor core (async proxy)
+          __syncwarp();
+          if (lane == 0) {
+            mbar_arrive(&s_empty[w]);
+            mbar_arrive(&p_full[w]);
+          }
+        }
+      }
+      // ---- row block finished: O = acc / l
+      mbar_wait(&o_done[w], od_ph, 19);
+      od_ph ^= 1;
+      tc_fence_after();
+      const float inv = raw ? 1.f : 1.f / l;  // l == 0 (fully masked row): inf -> NaN row, as in the reference
+      const uint32_t sbuf = sPw + q * 4096;   // this warp's own 32 rows of P k-chunk 0 double as staging tile
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        uint32_t r[32];
+        tmem_ld_32x32(tO + h * 32, r);
+        tmem_ld_wait();
+        tmem_ld_pin(r);
+        float v[32];
+#pragma unroll
+        for (int e = 0; e < 32; ++e) v[e] = __uint_as_float(r[e]) * inv;
+        stage_row32<T>(sbuf, lane, v, h);
+      }
+      tc_fence_before();
+      const int rows_valid = max(0, min(32, p.M - row0));
+      if (rows_valid > 0) {
+        if (p.o_tma_ok) {
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_5d(&p.tmO, sbuf, 0, 0, row0, b0i, b1i);
+            bulk_commit_group();
+            bulk_wait_group_read<0>();  // the staging rows are P rows of the next work item
+          }
+          __syncwarp();
+        } else {
+          __syncwarp();
+          T* dst = reinterpret_cast<T*>(p.O) + b1i * p.o_sb1 + b0i * p.o_sb0 + static_cast<long long>(row0) * p.ldo;
+          store_rows_generic<T>(sbuf, dst, p.ldo, rows_valid, p.dv, p.o_vec_ok != 0, lane);
+          __syncwarp();
+        }
+        if (p.lse != nullptr && row < p.M) p.lse[static_cast<size_t>(b) * p.M + row] = m_used + log2f(l);
+      }
+    }
+  }
+
+  // ---------------------------------------------------------- teardown
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, kAtTmemCols);
+  }
+  if (dist && do_consume && threadIdx.x == 0) {
+    // Last CTA out tells every peer that this rank no longer reads workspace parity (seq & 1).
+    __threadfence();
+    const uint32_t prev = atomicAdd(p.exit_counter, 1u);
+    if (prev == gridDim.x - 1) {
+      *p.exit_counter = 0;
+      __threadfence_system();
+      for (int i = 0; i < p.world; ++i) st_release_sys(p.done[i] + p.rank, p.seq);
+    }
+  }
+}
+
+}  // namespace ddp

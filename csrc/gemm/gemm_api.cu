@@ -10,6 +10,7 @@
 
 #include "../common/host_util.h"
 #include "gemm_sm100.cuh"
+#include "tma_map.h"
 
 namespace ddp {
 
@@ -34,8 +35,8 @@ static EncodeFn get_encode_fn() {
 static int elem_size(int dt) { return dt == DDP_F32 ? 4 : 2; }
 
 // dims/strides innermost first; strides in bytes for dims 1..4.
-static int make_map(CUtensorMap* m, int dt, void* ptr, const uint64_t dims[5], const uint64_t strides[4],
-                    const uint32_t box[5], bool mn_major) {
+int make_map(CUtensorMap* m, int dt, void* ptr, const uint64_t dims[5], const uint64_t strides[4],
+             const uint32_t box[5], bool mn_major) {
   EncodeFn enc = get_encode_fn();
   if (!enc) return set_error(-10, "cuTensorMapEncodeTiled is not available from the driver");
   // The encoder is a driver-API call and needs a current context on THIS thread.  A fresh thread (e.g. the

@@ -1,0 +1,394 @@
+// Standalone validation + timing harness for ddp_attn_fwd (no Python).  Runs on ONE GPU; multi-rank cases are
+// emulated like in gemm_harness.cu: every "rank" owns its workspace / flags on the same GPU, the produce phase of
+// all ranks runs before the consume phase.
+// Usage: attn_harness [quick|full|perf|one dt W b1 b0 M Tn d dv il maskmode chunk ramp dbg]
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/ddp_b200.h"
+
+#define CK(x)                                                                                 \
+  do {                                                                                        \
+    cudaError_t e_ = (x);                                                                     \
+    if (e_ != cudaSuccess) {                                                                  \
+      printf("CUDA error %s at %s:%d: %s\n", #x, __FILE__, __LINE__, cudaGetErrorString(e_)); \
+      exit(2);                                                                                \
+    }                                                                                         \
+  } while (0)
+
+static uint32_t g_seed = 777;
+static int irand(int lo, int hi) {
+  g_seed = g_seed * 1664525u + 1013904223u;
+  return lo + (int)((g_seed >> 8) % (uint32_t)(hi - lo + 1));
+}
+
+static void to_dev(const std::vector<float>& h, int dt, void* d) {
+  if (dt == DDP_BF16) {
+    std::vector<__nv_bfloat16> t(h.size());
+    for (size_t i = 0; i < h.size(); ++i) t[i] = __float2bfloat16(h[i]);
+    CK(cudaMemcpy(d, t.data(), t.size() * 2, cudaMemcpyHostToDevice));
+  } else {
+    std::vector<__half> t(h.size());
+    for (size_t i = 0; i < h.size(); ++i) t[i] = __float2half(h[i]);
+    CK(cudaMemcpy(d, t.data(), t.size() * 2, cudaMemcpyHostToDevice));
+  }
+}
+static std::vector<float> from_dev(const void* d, size_t n, int dt) {
+  std::vector<float> h(n);
+  if (dt == DDP_BF16) {
+    std::vector<__nv_bfloat16> t(n);
+    CK(cudaMemcpy(t.data(), d, n * 2, cudaMemcpyDeviceToHost));
+    for (size_t i = 0; i < n; ++i) h[i] = __bfloat162float(t[i]);
+  } else {
+    std::vector<__half> t(n);
+    CK(cudaMemcpy(t.data(), d, n * 2, cudaMemcpyDeviceToHost));
+    for (size_t i = 0; i < n; ++i) h[i] = __half2float(t[i]);
+  }
+  return h;
+}
+
+// Host tensor [b1][b0][rows][cols]; "interleave" = heads inside the row, like a [B, T, H*d] projection output.
+struct HT {
+  int b1, b0, rows, cols;
+  long long ld, sb0, sb1;
+  std::vector<float> v;
+  size_t size() const { return v.size(); }
+  float& at(int i1, int i0, int r, int c) { return v[i1 * sb1 + i0 * sb0 + (long long)r * ld + c]; }
+  float at(int i1, int i0, int r, int c) const { return v[i1 * sb1 + i0 * sb0 + (long long)r * ld + c]; }
+};
+static HT make_ht(int b1, int b0, int rows, int cols, bool interleave, bool fill, float mul = 0.25f) {
+  HT t;
+  t.b1 = b1; t.b0 = b0; t.rows = rows; t.cols = cols;
+  if (interleave) {
+    t.sb0 = cols; t.ld = (long long)b0 * cols; t.sb1 = t.ld * rows;
+  } else {
+    t.ld = cols; t.sb0 = t.ld * rows; t.sb1 = t.sb0 * b0;
+  }
+  t.v.assign((size_t)t.sb1 * b1, 0.f);
+  if (fill)
+    for (auto& x : t.v) x = irand(-8, 8) * mul;
+  return t;
+}
+static ddp_tensor dview(const HT& t, void* d, int dt) {
+  ddp_tensor x;
+  memset(&x, 0, sizeof x);
+  x.ptr = d; x.rows = t.rows; x.cols = t.cols; x.ld = t.ld; x.b0 = t.b0; x.b1 = t.b1; x.sb0 = t.sb0; x.sb1 = t.sb1;
+  x.dtype = dt;
+  return x;
+}
+
+struct Case {
+  int dt, world, b1, b0, M, Tn, d, dv;
+  bool interleave;
+  int maskmode;  // 0 none, 1 random 30 %, 2 block pattern with fully masked rows / tiles
+  int chunk;
+  int ramp;      // 1: later columns get larger scores (forces the lazy rescale of the O accumulator)
+};
+
+static int g_fail = 0, g_pass = 0;
+
+static bool run_case(const Case& c, int dbg, bool verbose) {
+  const int W = c.world, T = W * c.Tn;
+  const float scale = 1.0f / sqrtf((float)c.d);
+  std::vector<HT> A(W), B(W), V(W), O(W);
+  std::vector<std::vector<uint8_t>> mask(W);
+  for (int r = 0; r < W; ++r) {
+    A[r] = make_ht(c.b1, c.b0, c.M, c.d, c.interleave, true);
+    B[r] = make_ht(c.b1, c.b0, c.Tn, c.d, c.interleave, true);
+    V[r] = make_ht(c.b1, c.b0, c.Tn, c.dv, c.interleave, true);
+    O[r] = make_ht(c.b1, c.b0, c.M, c.dv, c.interleave, false);
+    if (c.ramp)
+      for (int i1 = 0; i1 < c.b1; ++i1)
+        for (int i0 = 0; i0 < c.b0; ++i0)
+          for (int j = 0; j < c.Tn; ++j) {
+            const int gcol = r * c.Tn + j;
+            const float f = (gcol * 4 / T) >= 2 ? 4.f : ((gcol * 4 / T) == 1 ? 2.f : 1.f);
+            for (int k = 0; k < c.d; ++k) B[r].at(i1, i0, j, k) *= f;
+          }
+    if (c.maskmode) {
+      mask[r].assign((size_t)c.b1 * c.M * T, 0);
+      for (int i1 = 0; i1 < c.b1; ++i1)
+        for (int m = 0; m < c.M; ++m)
+          for (int t = 0; t < T; ++t) {
+            uint8_t v = 0;
+            if (c.maskmode == 1) v = irand(0, 9) < 3;
+            if (c.maskmode == 2) v = (m % 37 == 5) || ((t / 128) % 3 == 1 && (m / 32) % 2 == 0) || (t > m + r * c.M);
+            mask[r][((size_t)i1 * c.M + m) * T + t] = v;
+          }
+    }
+  }
+  std::vector<void*> dA(W), dB(W), dV(W), dO(W), dMask(W, nullptr), dBits(W, nullptr), dLse(W);
+  const long long ldw = (T + 31) / 32;
+  for (int r = 0; r < W; ++r) {
+    CK(cudaMalloc(&dA[r], A[r].size() * 2));
+    CK(cudaMalloc(&dB[r], B[r].size() * 2));
+    CK(cudaMalloc(&dV[r], V[r].size() * 2));
+    CK(cudaMalloc(&dO[r], O[r].size() * 2));
+    CK(cudaMalloc(&dLse[r], (size_t)c.b1 * c.b0 * c.M * 4));
+    to_dev(A[r].v, c.dt, dA[r]);
+    to_dev(B[r].v, c.dt, dB[r]);
+    to_dev(V[r].v, c.dt, dV[r]);
+    CK(cudaMemset(dO[r], 0xFF, O[r].size() * 2));
+    CK(cudaMemset(dLse[r], 0xFF, (size_t)c.b1 * c.b0 * c.M * 4));
+    if (c.maskmode) {
+      CK(cudaMalloc(&dMask[r], mask[r].size()));
+      CK(cudaMemcpy(dMask[r], mask[r].data(), mask[r].size(), cudaMemcpyHostToDevice));
+      CK(cudaMalloc(&dBits[r], (size_t)c.b1 * c.M * ldw * 4));
+      if (ddp_pack_mask((const uint8_t*)dMask[r], c.b1, c.M, T, T, (long long)c.M * T, (uint32_t*)dBits[r], ldw, 0)) {
+        printf("pack_mask failed: %s\n", ddp_last_error());
+        return false;
+      }
+    }
+  }
+  std::vector<void*> ws(W, nullptr);
+  std::vector<uint32_t*> flags(W, nullptr), done(W, nullptr), exitc(W, nullptr);
+  if (W > 1) {
+    size_t wsb = 0, nf = 0;
+    ddp_tensor b0 = dview(B[0], dB[0], c.dt), v0 = dview(V[0], dV[0], c.dt);
+    ddp_attn_fwd_workspace(&b0, &v0, W, c.chunk, &wsb, &nf);
+    for (int r = 0; r < W; ++r) {
+      CK(cudaMalloc(&ws[r], wsb + 256));
+      CK(cudaMemset(ws[r], 0xFF, wsb + 256));
+      CK(cudaMalloc((void**)&flags[r], nf * 4 + 256));
+      CK(cudaMemset(flags[r], 0, nf * 4 + 256));
+      CK(cudaMalloc((void**)&done[r], 256));
+      CK(cudaMemset(done[r], 0, 256));
+      CK(cudaMalloc((void**)&exitc[r], 256));
+      CK(cudaMemset(exitc[r], 0, 256));
+    }
+  }
+  bool ok = true;
+  const int nseq = (W > 1) ? 2 : 1;
+  for (int s = 1; s <= nseq && ok; ++s) {
+    for (int phase = (W > 1 ? 1 : 3); phase <= (W > 1 ? 2 : 3); ++phase) {
+      for (int r = 0; r < W; ++r) {
+        ddp_comm cm;
+        memset(&cm, 0, sizeof cm);
+        cm.world = W; cm.rank = r; cm.seq = (uint32_t)s; cm.phase_mask = phase; cm.chunk_rows = c.chunk;
+        for (int q = 0; q < W; ++q) {
+          cm.ws[q] = ws[q]; cm.flags[q] = flags[q]; cm.done[q] = done[q];
+        }
+        cm.exit_counter = exitc[r];
+        ddp_tensor a = dview(A[r], dA[r], c.dt), b = dview(B[r], dB[r], c.dt), v = dview(V[r], dV[r], c.dt),
+                   o = dview(O[r], dO[r], c.dt);
+        int e = ddp_attn_fwd(&a, &b, &v, &o, (float*)dLse[r], (const uint32_t*)dBits[r], ldw, (long long)c.M * ldw, scale,
+                             W > 1 ? &cm : nullptr, dbg, 0);
+        if (e) {
+          printf("  ddp_attn_fwd error %d: %s\n", e, ddp_last_error());
+          ok = false;
+          break;
+        }
+      }
+      cudaError_t e = cudaDeviceSynchronize();
+      if (e != cudaSuccess) {
+        printf("  kernel fault: %s\n", cudaGetErrorString(e));
+        exit(3);
+      }
+      if (!ok) break;
+    }
+  }
+  const int site = ddp_debug_timeout_site_attn();
+  if (site) {
+    printf("  pipeline watchdog fired at site %d\n", site);
+    ok = false;
+  }
+  double max_err = 0, max_lse_err = 0;
+  long long nbad = 0, nshown = 0, nbad_lse = 0;
+  long long bad_wq[2][4] = {{0}}, bad_cg[2] = {0};
+  const bool raw = dbg & 1;
+  if (ok) {
+    const double sl2 = (double)scale * 1.4426950408889634;
+    std::vector<double> s(T), pj(T);
+    for (int r = 0; r < W; ++r) {
+      std::vector<float> got = from_dev(dO[r], O[r].size(), c.dt);
+      std::vector<float> lse((size_t)c.b1 * c.b0 * c.M);
+      CK(cudaMemcpy(lse.data(), dLse[r], lse.size() * 4, cudaMemcpyDeviceToHost));
+      for (int i1 = 0; i1 < c.b1; ++i1)
+        for (int i0 = 0; i0 < c.b0; ++i0)
+          for (int m = 0; m < c.M; ++m) {
+            double mx = -INFINITY;
+            for (int t = 0; t < T; ++t) {
+              const int src = t / c.Tn, j = t % c.Tn;
+              double acc = 0;
+              for (int k = 0; k < c.d; ++k) acc += (double)A[r].at(i1, i0, m, k) * B[src].at(i1, i0, j, k);
+              const bool dead = c.maskmode && mask[r][((size_t)i1 * c.M + m) * T + t];
+              s[t] = dead ? -INFINITY : acc * sl2;
+              if (s[t] > mx) mx = s[t];
+            }
+            double l = 0;
+            for (int t = 0; t < T; ++t) {
+              pj[t] = raw ? (s[t] == -INFINITY ? 0.0 : s[t]) : (mx == -INFINITY ? 0.0 : exp2(s[t] - mx));
+              l += pj[t];
+            }
+            const bool nan_row = !raw && (mx == -INFINITY);
+            for (int n = 0; n < c.dv; ++n) {
+              double ref = 0, mag = 0;
+              for (int t = 0; t < T; ++t) {
+                const double pv = pj[t] * V[t / c.Tn].at(i1, i0, t % c.Tn, n);
+                ref += pv;
+                mag += fabs(pv);
+              }
+              if (!raw) { ref /= l; mag /= l; }
+              const float g = got[i1 * O[r].sb1 + i0 * O[r].sb0 + (long long)m * O[r].ld + n];
+              bool bad;
+              double err = 0;
+              if (nan_row) {
+                bad = (g == g);  // must be NaN
+              } else {
+                err = fabs((double)g - ref);
+                bad = !(err <= 0.01 * mag + 0.01 * fabs(ref) + 2e-3);
+                if (err == err && err > max_err) max_err = err;
+              }
+              if (bad) {
+                ++nbad;
+                bad_wq[(m / 128) & 1][(m % 128) / 32]++;
+                bad_cg[(n / 32) & 1]++;
+                if (verbose && nshown < 8) {
+                  printf("    bad rank %d b(%d,%d) m %d n %d: got %g want %g%s\n", r, i1, i0, m, n, g, ref,
+                         nan_row ? " (NaN row)" : "");
+                  ++nshown;
+                }
+              }
+            }
+            if (!raw && !nan_row) {
+              const double lref = mx + log2(l);
+              const double e = fabs((double)lse[((size_t)i1 * c.b0 + i0) * c.M + m] - lref);
+              if (!(e <= 2e-2)) {
+                ++nbad_lse;
+                if (verbose && nbad_lse <= 4)
+                  printf("    bad lse rank %d b(%d,%d) m %d: got %g want %g\n", r, i1, i0, m,
+                         lse[((size_t)i1 * c.b0 + i0) * c.M + m], lref);
+              }
+              if (e == e && e > max_lse_err) max_lse_err = e;
+            }
+          }
+    }
+    if (nbad || nbad_lse) ok = false;
+  }
+  printf("%s ATTN %s W=%d b=(%d,%d) M=%d Tn=%d d=%d dv=%d il=%d mask=%d chunk=%d ramp=%d dbg=%d  max_err=%.3g bad=%lld "
+         "lse_err=%.3g bad_lse=%lld\n",
+         ok ? "PASS" : "FAIL", c.dt == DDP_BF16 ? "bf16" : "fp16", W, c.b1, c.b0, c.M, c.Tn, c.d, c.dv, (int)c.interleave,
+         c.maskmode, c.chunk, c.ramp, dbg, max_err, nbad, max_lse_err, nbad_lse);
+  if (nbad)
+    printf("    bad by (row block, quadrant): [%lld %lld %lld %lld] [%lld %lld %lld %lld]  by column half: %lld %lld\n",
+           bad_wq[0][0], bad_wq[0][1], bad_wq[0][2], bad_wq[0][3], bad_wq[1][0], bad_wq[1][1], bad_wq[1][2], bad_wq[1][3],
+           bad_cg[0], bad_cg[1]);
+  fflush(stdout);
+  for (int r = 0; r < W; ++r) {
+    cudaFree(dA[r]); cudaFree(dB[r]); cudaFree(dV[r]); cudaFree(dO[r]); cudaFree(dLse[r]);
+    if (dMask[r]) cudaFree(dMask[r]);
+    if (dBits[r]) cudaFree(dBits[r]);
+    if (W > 1) { cudaFree(ws[r]); cudaFree(flags[r]); cudaFree(done[r]); cudaFree(exitc[r]); }
+  }
+  if (ok) ++g_pass; else ++g_fail;
+  return ok;
+}
+
+static void perf_case(int dt, int H, int M, int Tn, int d, bool with_mask, int iters, int dbg = 0) {
+  HT A = make_ht(1, H, M, d, true, false), B = make_ht(1, H, Tn, d, true, false), V = make_ht(1, H, Tn, d, true, false),
+     O = make_ht(1, H, M, d, true, false);
+  void *dA, *dB, *dV, *dO, *dBits = nullptr;
+  float* dLse;
+  CK(cudaMalloc(&dA, A.size() * 2));
+  CK(cudaMalloc(&dB, B.size() * 2));
+  CK(cudaMalloc(&dV, V.size() * 2));
+  CK(cudaMalloc(&dO, O.size() * 2));
+  CK(cudaMalloc((void**)&dLse, (size_t)H * M * 4));
+  // small deterministic values: 0x3c3c as bf16 is ~0.0115
+  CK(cudaMemset(dA, 0x3c, A.size() * 2));
+  CK(cudaMemset(dB, 0x3c, B.size() * 2));
+  CK(cudaMemset(dV, 0x3c, V.size() * 2));
+  const long long ldw = (Tn + 31) / 32;
+  if (with_mask) {
+    CK(cudaMalloc(&dBits, (size_t)M * ldw * 4));
+    CK(cudaMemset(dBits, 0, (size_t)M * ldw * 4));
+  }
+  ddp_tensor a = dview(A, dA, dt), b = dview(B, dB, dt), v = dview(V, dV, dt), o = dview(O, dO, dt);
+  const float scale = 1.0f / sqrtf((float)d);
+  cudaEvent_t e0, e1;
+  CK(cudaEventCreate(&e0));
+  CK(cudaEventCreate(&e1));
+  for (int i = 0; i < 2; ++i)
+    if (ddp_attn_fwd(&a, &b, &v, &o, dLse, (const uint32_t*)dBits, ldw, (long long)M * ldw, scale, nullptr, dbg, 0)) {
+      printf("perf launch failed: %s\n", ddp_last_error());
+      return;
+    }
+  CK(cudaDeviceSynchronize());
+  CK(cudaEventRecord(e0));
+  for (int i = 0; i < iters; ++i)
+    ddp_attn_fwd(&a, &b, &v, &o, dLse, (const uint32_t*)dBits, ldw, (long long)M * ldw, scale, nullptr, dbg, 0);
+  CK(cudaEventRecord(e1));
+  CK(cudaEventSynchronize(e1));
+  float ms;
+  CK(cudaEventElapsedTime(&ms, e0, e1));
+  ms /= iters;
+  const double flops = 4.0 * H * (double)M * Tn * d;
+  const int site = ddp_debug_timeout_site_attn();
+  printf("PERF ATTN %s H=%d M=%d T=%d d=%d mask=%d dbg=%d: %.3f ms  %.1f TFLOP/s  (%.0f clk per 128x128 tile and SM)%s\n",
+         dt == DDP_BF16 ? "bf16" : "fp16", H, M, Tn, d, (int)with_mask, dbg, ms, flops / ms * 1e-9,
+         ms * 1e-3 * 1.965e9 * 148.0 / ((double)H * (M / 128.0) * (Tn / 128.0)), site ? "  WATCHDOG FIRED" : "");
+  fflush(stdout);
+  cudaFree(dA); cudaFree(dB); cudaFree(dV); cudaFree(dO); cudaFree(dLse);
+  if (dBits) cudaFree(dBits);
+}
+
+int main(int argc, char** argv) {
+  std::string mode = argc > 1 ? argv[1] : "quick";
+  cudaDeviceProp prop;
+  CK(cudaGetDeviceProperties(&prop, 0));
+  printf("device: %s sm_%d%d, %d SMs\n", prop.name, prop.major, prop.minor, prop.multiProcessorCount);
+  if (mode == "one" && argc >= 14) {
+    Case c;
+    c.dt = atoi(argv[2]); c.world = atoi(argv[3]); c.b1 = atoi(argv[4]); c.b0 = atoi(argv[5]); c.M = atoi(argv[6]);
+    c.Tn = atoi(argv[7]); c.d = atoi(argv[8]); c.dv = atoi(argv[9]); c.interleave = atoi(argv[10]) != 0;
+    c.maskmode = atoi(argv[11]); c.chunk = atoi(argv[12]); c.ramp = atoi(argv[13]);
+    run_case(c, argc > 14 ? atoi(argv[14]) : 0, true);
+    return g_fail ? 1 : 0;
+  }
+  if (mode != "perf") {
+    const int bf = DDP_BF16;
+    //        dt  W b1 b0 M    Tn   d   dv  il     mask chunk ramp
+    // stage 1: linear mode (no max / exp): isolates S MMA -> P staging -> PV MMA -> O store
+    if (!run_case({bf, 1, 1, 1, 256, 128, 64, 64, false, 0, 64, 0}, 1, true)) {
+      run_case({bf, 1, 1, 1, 256, 128, 64, 64, false, 0, 64, 0}, 1 | 16, true);  // generic O stores
+      run_case({bf, 1, 1, 1, 256, 128, 64, 64, false, 0, 64, 0}, 0, true);
+      printf("SUMMARY pass=%d fail=%d (stopped early)\n", g_pass, g_fail);
+      return 1;
+    }
+    if (!run_case({bf, 1, 1, 1, 256, 384, 64, 64, false, 0, 64, 0}, 1, true)) {
+      printf("SUMMARY pass=%d fail=%d (stopped early)\n", g_pass, g_fail);
+      return 1;
+    }
+    // stage 2: the real thing
+    run_case({bf, 1, 1, 1, 256, 128, 64, 64, false, 0, 64, 0}, 0, true);
+    run_case({bf, 1, 1, 1, 256, 512, 64, 64, false, 0, 64, 0}, 0, true);
+    run_case({bf, 1, 1, 1, 256, 512, 64, 64, false, 0, 64, 1}, 0, true);   // lazy rescale
+    run_case({bf, 1, 1, 2, 512, 640, 64, 64, true, 1, 64, 1}, 0, true);    // heads interleaved, random mask
+    run_case({bf, 1, 2, 3, 200, 300, 32, 32, true, 2, 64, 1}, 0, true);    // ragged, fully masked rows / tiles
+    run_case({bf, 1, 1, 2, 100, 72, 40, 24, false, 1, 64, 0}, 0, true);    // d != dv, everything ragged
+    run_case({DDP_F16, 1, 1, 2, 384, 256, 64, 64, true, 1, 64, 0}, 0, true);
+    run_case({bf, 1, 1, 4, 1024, 1024, 64, 64, true, 0, 64, 0}, 0, true);  // several items per CTA? (32 items)
+    // stage 3: emulated ranks
+    if (mode == "full" || mode == "quick") {
+      run_case({bf, 2, 1, 2, 256, 256, 64, 64, true, 0, 64, 0}, 0, true);
+      run_case({bf, 2, 1, 2, 256, 256, 64, 64, true, 1, 128, 1}, 0, true);
+      run_case({bf, 4, 2, 2, 160, 160, 32, 32, true, 2, 64, 1}, 0, true);
+      run_case({bf, 4, 1, 3, 100, 96, 64, 64, false, 1, 32, 0}, 0, true);
+    }
+    printf("SUMMARY pass=%d fail=%d\n", g_pass, g_fail);
+  }
+  if (mode == "perf" || mode == "full") {
+    perf_case(DDP_BF16, 16, 8192, 8192, 64, false, 5);
+    perf_case(DDP_BF16, 16, 8192, 8192, 64, true, 5);
+    perf_case(DDP_BF16, 16, 8192, 8192, 64, false, 5, 1);  // linear mode: MMA + staging without the exponentials
+  }
+  return g_fail ? 1 : 0;
+}

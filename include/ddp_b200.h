@@ -107,6 +107,23 @@ int ddp_softmax_combine(const void* stats, int64_t n_rows, int32_t nt, void* row
 int ddp_gemm_ex(int op, const ddp_tensor* A, const ddp_tensor* B, const ddp_tensor* C, float alpha,
                 const void* bias, const ddp_comm* comm, const ddp_epilogue* epi, int dbg, void* stream);
 
+/* Slab-free attention forward (module.py:61-69 in ONE kernel, all-gather of B and V fused in):
+ *     O = softmax(scale * A . gather(B)^T, mask) . gather(V)
+ * A = [b1][b0][M][d] (this rank's rows; the reference's keys), B = [b1][b0][Tn][d] and V = [b1][b0][Tn][dv] (this
+ * rank's share of the column-side operands; the reference's queries / values), O = [b1][b0][M][dv].  bf16 / fp16,
+ * d and dv multiples of 8 and <= 64, scale > 0.  Scores stay in TMEM, probabilities go through shared memory
+ * back into the tensor core (online softmax); the [M x T] slab is never written.  lse (optional, fp32
+ * [b1][b0][M]) receives log2(sum_j exp(scale * s_ij)) = row max + log2(row sum) in the log2 domain.
+ * mask_bits as for the softmax epilogues (ddp_pack_mask; bit set = masked out; NULL = no mask); a fully masked
+ * row is NaN as in the reference.  comm as for ddp_gemm (workspace / flag sizes: ddp_attn_fwd_workspace).
+ * Errors -6: shape or dtype outside what this kernel covers (callers fall back to the three-kernel path). */
+int ddp_attn_fwd_workspace(const ddp_tensor* B, const ddp_tensor* V, int world, int chunk_rows, size_t* ws_bytes,
+                           size_t* n_flags);
+int ddp_attn_fwd(const ddp_tensor* A, const ddp_tensor* B, const ddp_tensor* V, const ddp_tensor* O, float* lse,
+                 const uint32_t* mask_bits, int64_t mask_ld_words, int64_t mask_sb1_words, float scale,
+                 const ddp_comm* comm, int dbg, void* stream);
+int ddp_debug_timeout_site_attn(void); /* pipeline watchdog of the attention kernel (sites 11-19) */
+
 /* Row softmax over the last dim of x[b1][b0][rows][cols] with fused scale and boolean mask:
  *   y = softmax(scale * x  masked_fill(mask, -inf))     (reference: module.py:65-67)
  * mask is uint8 [b1][rows][cols] (broadcast over b0 = heads), nonzero = masked out; may be NULL.
