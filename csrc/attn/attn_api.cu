@@ -12,7 +12,7 @@
 namespace ddp {
 
 constexpr int kAtStages = 3;
-constexpr int kAtSmem = 2 * kAtTile + 2 * kAtPBytes + kAtStages * kAtStageBytes + (2 * kAtStages + 10) * 8 + 16 + 1024;
+constexpr int kAtSmem = 2 * kAtTile + 2 * kAtPBytes + kAtStages * kAtStageBytes + (2 * kAtStages + 14) * 8 + 16 + 4 * 128 * 8 + 1024;
 static_assert(kAtSmem <= 232448, "shared memory budget exceeded");
 
 static int attn_check(const ddp_tensor* A, const ddp_tensor* B, const ddp_tensor* V, int world) {
@@ -43,14 +43,14 @@ static int tile_map(CUtensorMap* m, const ddp_tensor* t, uint32_t box_rows, bool
 
 template <int DT>
 static int attn_launch(const AttnKParams& p, int grid, cudaStream_t stream) {
-  auto kern = attn_fwd_kernel<DT, kAtStages>;
-  static bool configured[64] = {};
+  auto kern = (p.dbg & 1) ? attn_fwd_kernel<DT, kAtStages, true> : attn_fwd_kernel<DT, kAtStages, false>;
+  static bool configured[2][64] = {};
   int dev = 0;
   cudaGetDevice(&dev);
-  if (dev < 64 && !configured[dev]) {
+  if (dev < 64 && !configured[p.dbg & 1][dev]) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kAtSmem);
     if (e != cudaSuccess) return set_error(-12, cudaGetErrorString(e));
-    configured[dev] = true;
+    configured[p.dbg & 1][dev] = true;
   }
   kern<<<grid, kAtThreads, kAtSmem, stream>>>(p);
   cudaError_t e = cudaGetLastError();

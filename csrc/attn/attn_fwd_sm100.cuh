@@ -9,25 +9,31 @@
 //
 //   warp 0      TMA producer: A tiles (two 128-row blocks per work item) and a ring of (B_j, V_j) column blocks;
 //               polls the peers' per-chunk flags before touching gathered rows
-//   warp 1      MMA issuer:   S_w = A_w . B_j^T (128x128, K = d) and O_w += P_w . V_j (128 x dv, K = 128) for the
-//               two row blocks w = 0, 1, interleaved so that one block's softmax overlaps the other's MMAs
+//   warp 1      MMA issuer:   S_w = A_w . B_j^T (128x128, K = d) for the two row blocks w = 0, 1 and, per row block,
+//               TWO independent accumulators O_{w,h} += P_w[:, half h] . V_j[half h] (128 x dv, K = 64); event
+//               driven, so S_w(j+1) is computed while the softmax warps are still busy with step j
 //   warps 2-3   TMEM alloc; all-gather pushers (B and V chunks -> every peer's workspace, one flag per chunk)
-//   warps 4-7   softmax warpgroup of row block 0 (thread = row): TMEM S -> max / exp2 / sum -> bf16 P in smem,
-//   warps 8-11  same for row block 1;  rescales the O accumulator in TMEM only when the running max moved by
-//               more than 2^8 (lazy rescale), normalises and stores O at the end of the row block.
+//   warps 4-19  softmax: warp = (row block w, column half h, lane quadrant q), thread = one row x 64 columns held
+//               in registers.  Every (row, half) is its own online-softmax stream (own running max and sum, own
+//               O accumulator), so no per-step exchange between the two threads of a row is needed; the two
+//               streams are merged once, when the row block is finished.  The running max only moves when it grew
+//               by more than 2^8 (lazy rescale of the O accumulator in TMEM).  Four softmax warps per scheduler
+//               keep the MUFU pipe (ex2, the bound of this kernel at head dim 64) busy.
 #pragma once
 #include "../gemm/gemm_sm100.cuh"
 
 namespace ddp {
 
-constexpr int kAtThreads = 384;
+constexpr int kAtThreads = 640;
 constexpr int kAtBM = 128;                 // rows per warpgroup tile
 constexpr int kAtBN = 128;                 // columns per step
 constexpr int kAtTile = 128 * 128;         // 128 rows x 128 bytes
 constexpr int kAtPBytes = 2 * kAtTile;     // P tile of one warpgroup: two 64-column k-chunks
 constexpr int kAtStageBytes = 2 * kAtTile; // B_j | V_j
-constexpr uint32_t kAtTmemCols = 512;      // S0 S1 (128 each) | O0 O1 (64 each)
+constexpr uint32_t kAtTmemCols = 512;      // S0 S1 (128 each) | O00 O01 O10 O11 (64 each)
 constexpr float kAtTau = 8.f;              // lazy-rescale threshold (log2 units)
+constexpr int kAtRegsLow = 56;             // registers per thread of warps 0-3 after setmaxnreg
+constexpr int kAtRegsHigh = 104;           // ... of the softmax warps (128 x 56 + 512 x 104 <= 640 x 96)
 
 struct alignas(64) AttnKParams {
   CUtensorMap tmA;   // [b1][b0][M][d]     box 64 x 128 rows
@@ -64,7 +70,7 @@ struct alignas(64) AttnKParams {
   int dbg;  // bit 0 (harness): P = scale_log2 * S without max / exp / normalisation (linear, isolates the MMAs)
 };
 
-template <int DT, int STAGES>
+template <int DT, int STAGES, bool kRaw = false>
 __global__ void __launch_bounds__(kAtThreads, 1) attn_fwd_kernel(const __grid_constant__ AttnKParams p) {
   using T = typename std::conditional<DT == DDP_BF16, __nv_bfloat16, __half>::type;
   static_assert(DT == DDP_BF16 || DT == DDP_F16, "16-bit operands only");
@@ -81,9 +87,10 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_fwd_kernel(const __grid_co
   uint64_t* a_empty = a_full + 1;           // [1]
   uint64_t* s_full = a_empty + 1;           // [2]  S_w landed in TMEM
   uint64_t* s_empty = s_full + 2;           // [2]  warpgroup w has read S_w
-  uint64_t* p_full = s_empty + 2;           // [2]  P_w staged (and O_w rescaled)
-  uint64_t* o_done = p_full + 2;            // [2]  O_w += P_w V_j finished
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_done + 2);
+  uint64_t* p_full = s_empty + 2;           // [4]  half h of P_w staged (and O_{w,h} rescaled); index w*2+h
+  uint64_t* o_done = p_full + 4;            // [4]  O_{w,h} += P_{w,h} V_j finished
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_done + 4);
+  float2* sStat = reinterpret_cast<float2*>(tmem_slot + 4);  // [2][2][128] (max, sum) of every stream, for the merge
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -113,9 +120,11 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_fwd_kernel(const __grid_co
     mbar_init(a_empty, 1);
     for (int w = 0; w < 2; ++w) {
       mbar_init(&s_full[w], 1);
-      mbar_init(&s_empty[w], 4);
-      mbar_init(&p_full[w], 4);
-      mbar_init(&o_done[w], 1);
+      mbar_init(&s_empty[w], 8);
+    }
+    for (int st = 0; st < 4; ++st) {
+      mbar_init(&p_full[st], 4);
+      mbar_init(&o_done[st], 1);
     }
     fence_mbar_init();
   }
@@ -135,6 +144,11 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_fwd_kernel(const __grid_co
     m0 = pair * (2 * kAtBM);
   };
 
+  // The softmax threads keep a whole 128-column score row in registers: the producer / MMA / pusher warpgroup
+  // hands most of its registers to the two softmax warpgroups (setmaxnreg; the two sides only meet again at the
+  // teardown, so the compiler allocates each side with its own budget).
+  if (warp < 4) {
+  setmaxnreg_dec<kAtRegsLow>();
   if (warp == 0) {
     // ======================================================= TMA producer (whole warp walks the loop)
     int stage = 0;
@@ -190,64 +204,93 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_fwd_kernel(const __grid_co
       }
     }
   } else if (warp == 1) {
-    // ======================================================= MMA issuer
+    // ======================================================= MMA issuer (event driven)
+    // A softmax warpgroup releases S_w as soon as the row sits in its registers, so S_w(j+1) is computed while
+    // the warpgroup still works on step j; the single issuing thread therefore polls the four conditions
+    // (S_w buffer free + operands landed, P_w staged; w = 0, 1) and issues whatever has become possible.
     if (lane == 0) {
       constexpr uint32_t kIdS = umma_idesc(DT, 0u, 0u, kAtBM, kAtBN);  // A K-major, B K-major
       constexpr uint32_t kIdO = umma_idesc(DT, 0u, 1u, kAtBM, 64);     // A = P K-major, B = V MN-major
-      int stage = 0;
-      uint32_t ph = 0, a_ph = 0;
-      uint32_t se_ph0 = 0, se_ph1 = 0, pf_ph0 = 0, pf_ph1 = 0;
+      uint32_t a_ph = 0;
+      uint32_t se_ph[2] = {0u, 0u}, pf_ph[4] = {0u, 0u, 0u, 0u};
       const uint32_t sA_u = smem_u32(sA), sP_u = smem_u32(sP), sKV_u = smem_u32(sKV);
-      auto issue_S = [&](int w, uint32_t sb) {
-        uint32_t& se = w ? se_ph1 : se_ph0;
-        mbar_wait(&s_empty[w], se ^ 1, 13);
-        se ^= 1;
-        tc_fence_after();
-#pragma unroll
-        for (int kk = 0; kk < 4; ++kk)
-          umma_ss<false>(tmem_base + w * kAtBN, umma_smem_desc(sA_u + w * kAtTile + kk * 32, 16, 1024),
-                         umma_smem_desc(sb + kk * 32, 16, 1024), kIdS, kk != 0 ? 1u : 0u);
-        umma_commit(&s_full[w]);
-      };
+      uint32_t g0 = 0;  // steps issued by earlier work items: step j of this item uses ring slot (g0 + j) % STAGES
       for (int it = blockIdx.x; it < items; it += gridDim.x) {
         mbar_wait(a_full, a_ph, 14);
         a_ph ^= 1;
-        mbar_wait(&kv_full[stage], ph, 15);
         tc_fence_after();
-        issue_S(0, sKV_u + stage * kAtStageBytes);
-        issue_S(1, sKV_u + stage * kAtStageBytes);
-        for (int j = 0; j < nj; ++j) {
-          const uint32_t sv = sKV_u + stage * kAtStageBytes + kAtTile;
-          const int nstage = (stage + 1 == STAGES) ? 0 : stage + 1;
-          const uint32_t nph = (nstage == 0) ? (ph ^ 1) : ph;
+        int nS[2] = {0, 0}, nPV[4] = {0, 0, 0, 0};
+        int kvr = 0;       // steps of this item whose operands are known to have landed
+        int released = 0;  // steps whose ring slot went back to the producer
+        uint32_t spins = 0;
+        uint64_t t0 = 0;
+        while (released < nj) {
+          bool progress = false;
 #pragma unroll
           for (int w = 0; w < 2; ++w) {
-            uint32_t& pf = w ? pf_ph1 : pf_ph0;
-            mbar_wait(&p_full[w], pf, 16);
-            pf ^= 1;
-            tc_fence_after();
-#pragma unroll
-            for (int kk = 0; kk < 8; ++kk)
-              umma_ss<false>(tmem_base + 2 * kAtBN + w * 64,
-                             umma_smem_desc(sP_u + w * kAtPBytes + (kk >> 2) * kAtTile + (kk & 3) * 32, 16, 1024),
-                             umma_smem_desc(sv + kk * 2048, kAtTile, 1024, 2), kIdO, (j | kk) != 0 ? 1u : 0u);
-            umma_commit(&o_done[w]);
-            if (j + 1 < nj) {
-              if (w == 0) {
-                mbar_wait(&kv_full[nstage], nph, 15);
+            if (nS[w] < nj) {
+              const int j = nS[w];
+              const uint32_t g = g0 + j;
+              if (j >= kvr && mbar_try_wait(&kv_full[g % STAGES], (g / STAGES) & 1)) kvr = j + 1;
+              if (j < kvr && mbar_try_wait(&s_empty[w], se_ph[w] ^ 1)) {
+                se_ph[w] ^= 1;
                 tc_fence_after();
+                const uint32_t sb = sKV_u + (g % STAGES) * kAtStageBytes;
+#pragma unroll
+                for (int kk = 0; kk < 4; ++kk)
+                  umma_ss<false>(tmem_base + w * kAtBN, umma_smem_desc(sA_u + w * kAtTile + kk * 32, 16, 1024),
+                                 umma_smem_desc(sb + kk * 32, 16, 1024), kIdS, kk != 0 ? 1u : 0u);
+                umma_commit(&s_full[w]);
+                nS[w] = j + 1;
+                progress = true;
               }
-              issue_S(w, sKV_u + nstage * kAtStageBytes);
+            }
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+              const int st = w * 2 + h;
+              if (nPV[st] < nS[w] && mbar_try_wait(&p_full[st], pf_ph[st])) {
+                pf_ph[st] ^= 1;
+                tc_fence_after();
+                const int j = nPV[st];
+                const uint32_t g = g0 + j;
+                const uint32_t sv = sKV_u + (g % STAGES) * kAtStageBytes + kAtTile + h * (4 * 2048);
+                const uint32_t sp = sP_u + w * kAtPBytes + h * kAtTile;
+#pragma unroll
+                for (int kk = 0; kk < 4; ++kk)
+                  umma_ss<false>(tmem_base + 2 * kAtBN + st * 64, umma_smem_desc(sp + kk * 32, 16, 1024),
+                                 umma_smem_desc(sv + kk * 2048, kAtTile, 1024, 2), kIdO, (j | kk) != 0 ? 1u : 0u);
+                umma_commit(&o_done[st]);
+                nPV[st] = j + 1;
+                progress = true;
+              }
             }
           }
-          umma_commit(&kv_empty[stage]);
-          stage = nstage;
-          ph = nph;
+          // all four streams are through with column block `released`: its ring slot goes back to the producer
+          const int lo = min(min(nPV[0], nPV[1]), min(nPV[2], nPV[3]));
+          while (released < lo) {
+            umma_commit(&kv_empty[(g0 + released) % STAGES]);
+            ++released;
+          }
+          if (progress) {
+            spins = 0;
+            t0 = 0;
+          } else if ((++spins & 0xFFFu) == 0) {
+            // same watchdog as mbar_wait: a broken pipeline must not hang the GPU
+            const uint64_t now = global_timer_ns();
+            if (t0 == 0) {
+              t0 = now;
+            } else if (now - t0 > 4000000000ull) {
+              atomicMax(&g_ddp_timeout_site, 16u);
+              break;
+            }
+            if (*reinterpret_cast<volatile unsigned int*>(&g_ddp_timeout_site) != 0) break;
+          }
         }
         umma_commit(a_empty);
+        g0 += static_cast<uint32_t>(nj);
       }
     }
-  } else if (warp < 4) {
+  } else {
     // ======================================================= all-gather pushers (B and V)
     if (dist && do_produce) {
       const int gw = blockIdx.x * 2 + (warp - 2);
@@ -308,16 +351,23 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_fwd_kernel(const __grid_co
         __syncwarp();
       }
     }
+  }
   } else {
-    // ======================================================= softmax warpgroups (thread = row)
-    const int w = (warp - 4) >> 2;  // row block of the pair
-    const int q = warp & 3;         // TMEM lane quadrant this warp may access (= warp id mod 4)
+    setmaxnreg_inc<kAtRegsHigh>();
+    // ======================================================= softmax warps (thread = one row x 64 columns)
+    const int idx = warp - 4;
+    const int q = idx & 3;         // TMEM lane quadrant this warp may access (= warp id mod 4)
+    const int h = (idx >> 2) & 1;  // column half of every step
+    const int w = idx >> 3;        // row block of the pair
+    const int st = w * 2 + h;      // stream
     const int row_in = q * 32 + lane;
-    const uint32_t tS = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + w * kAtBN;
-    const uint32_t tO = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + 2 * kAtBN + w * 64;
+    const uint32_t lane_base = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+    const uint32_t tS = lane_base + w * kAtBN + h * 64;
+    const uint32_t tO = lane_base + 2 * kAtBN + st * 64;
     const uint32_t sPw = smem_u32(sP) + w * kAtPBytes;
+    const uint32_t sPh = sPw + h * kAtTile + row_in * 128;  // this thread's 128-byte row of P k-chunk h
     const uint32_t sw = lane & 7;
-    const bool raw = (p.dbg & 1) != 0;
+    const uint32_t pair_bar = 1 + w * 4 + q;  // named barrier shared with the warp of the other column half
     uint32_t sf_ph = 0, od_ph = 0;
     for (int it = blockIdx.x; it < items; it += gridDim.x) {
       int b1i, b0i, m0;
@@ -333,21 +383,19 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_fwd_kernel(const __grid_co
       for (int si = 0; si < p.world; ++si) {
         const int seg = (p.rank + si) % p.world;
         for (int nb = 0; nb < p.n_blocks; ++nb, ++j) {
-          const int n0 = nb * kAtBN;
-          const int nvalid = min(kAtBN, p.Tn - n0);
-          // mask words of this row for the 128 columns of the step (bit set = masked out), fetched before the
-          // wait so that their latency hides behind the MMA
-          uint32_t mk[4] = {0u, 0u, 0u, 0u};
+          const int n0 = nb * kAtBN + h * 64;                  // first column of this thread's half
+          const int nvalid = max(0, min(64, p.Tn - n0));
+          // mask words of this row for the 64 columns (bit set = masked out), fetched before the wait so that
+          // their latency hides behind the MMA
+          uint32_t mk[2] = {0u, 0u};
           if (mrow != nullptr) {
             const uint32_t* mp = mrow + ((static_cast<long long>(seg) * p.Tn + n0) >> 5);
-            const int nw = (nvalid + 31) >> 5;
-#pragma unroll
-            for (int i = 0; i < 4; ++i)
-              if (i < nw) mk[i] = __ldg(mp + i);
+            if (nvalid > 0) mk[0] = __ldg(mp);
+            if (nvalid > 32) mk[1] = __ldg(mp + 1);
           }
-          if (nvalid < kAtBN) {
+          if (nvalid < 64) {
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
+            for (int i = 0; i < 2; ++i) {
               const int lo = i * 32;
               if (nvalid <= lo) {
                 mk[i] = 0xffffffffu;
@@ -359,70 +407,77 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_fwd_kernel(const __grid_co
           mbar_wait(&s_full[w], sf_ph, 17);
           sf_ph ^= 1;
           tc_fence_after();
-          // ---- pass A: row maximum of the raw scores over the live columns
-          float mx = -INFINITY;
+          // ---- this thread's half row: one TMEM load, then S_w goes straight back to the MMA warp
+          uint32_t r[64];
+          tmem_ld_32x64(tS, r);
+          tmem_ld_wait();
+          tmem_ld_pin64(r);
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&s_empty[w]);
+          // ---- maximum of the raw scores over the live columns (four independent chains)
+          float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
 #pragma unroll
-          for (int c = 0; c < 4; ++c) {
-            uint32_t r[32];
-            tmem_ld_32x32(tS + c * 32, r);
-            tmem_ld_wait();
-            tmem_ld_pin(r);
+          for (int c = 0; c < 2; ++c) {
             if (mk[c] == 0u) {
 #pragma unroll
-              for (int e = 0; e < 32; ++e) mx = fmaxf(mx, __uint_as_float(r[e]));
+              for (int e = 0; e < 32; e += 4) {
+                mx0 = fmaxf(mx0, __uint_as_float(r[c * 32 + e]));
+                mx1 = fmaxf(mx1, __uint_as_float(r[c * 32 + e + 1]));
+                mx2 = fmaxf(mx2, __uint_as_float(r[c * 32 + e + 2]));
+                mx3 = fmaxf(mx3, __uint_as_float(r[c * 32 + e + 3]));
+              }
             } else {
 #pragma unroll
               for (int e = 0; e < 32; ++e)
-                if (!((mk[c] >> e) & 1u)) mx = fmaxf(mx, __uint_as_float(r[e]));
+                if (!((mk[c] >> e) & 1u)) mx0 = fmaxf(mx0, __uint_as_float(r[c * 32 + e]));
             }
           }
-          const float m_blk = mx * p.scale_log2;  // scale_log2 > 0; -inf stays -inf
+          const float m_blk = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3)) * p.scale_log2;  // scale_log2 > 0
           // Lazy rescale: the reference point of the exponentials only moves when the maximum grew by more than
           // 2^kAtTau, so P stays <= 2^kAtTau and the O accumulator is rarely touched.
-          const bool need = !raw && (m_blk > m_used + kAtTau);
+          const bool need = !kRaw && (m_blk > m_used + kAtTau);
           if (j > 0) {
-            // O_w += P_w V_{j-1} has finished: P_w may be overwritten, O_w may be rescaled
-            mbar_wait(&o_done[w], od_ph, 18);
+            // O_st += P V_{j-1} has finished: our P rows may be overwritten, O_st may be rescaled
+            mbar_wait(&o_done[st], od_ph, 18);
             od_ph ^= 1;
             tc_fence_after();
             if (__any_sync(0xffffffffu, need)) {
               const float f = need ? ex2_approx(m_used - m_blk) : 1.f;
 #pragma unroll
-              for (int h = 0; h < 2; ++h) {
-                uint32_t r[32];
-                tmem_ld_32x32(tO + h * 32, r);
+              for (int hh = 0; hh < 2; ++hh) {
+                uint32_t ro[32];
+                tmem_ld_32x32(tO + hh * 32, ro);
                 tmem_ld_wait();
-                tmem_ld_pin(r);
+                tmem_ld_pin(ro);
 #pragma unroll
-                for (int e = 0; e < 32; ++e) r[e] = __float_as_uint(__uint_as_float(r[e]) * f);
-                tmem_st_32x32(tO + h * 32, r);
+                for (int e = 0; e < 32; ++e) ro[e] = __float_as_uint(__uint_as_float(ro[e]) * f);
+                tmem_st_32x32(tO + hh * 32, ro);
               }
               tmem_st_wait();
               l *= f;
             }
           }
           if (need) m_used = m_blk;
-          const float neg_m = (raw || m_used == -INFINITY) ? 0.f : -m_used;
-          // ---- pass B: P = exp2(scale_log2 * S - m) -> bf16 tile in shared memory (K-major, 128B swizzle)
+          const float neg_m = (kRaw || m_used == -INFINITY) ? 0.f : -m_used;
+          // ---- P = exp2(scale_log2 * S - m) -> bf16 row in shared memory (K-major, 128B swizzle)
           float l0 = 0.f, l1 = 0.f, l2 = 0.f, l3 = 0.f;
 #pragma unroll
-          for (int c = 0; c < 4; ++c) {
-            uint32_t r[32];
-            tmem_ld_32x32(tS + c * 32, r);
-            tmem_ld_wait();
-            tmem_ld_pin(r);
+          for (int c = 0; c < 2; ++c) {
             float v[32];
-            if (raw) {
+            if (kRaw) {
 #pragma unroll
               for (int e = 0; e < 32; ++e)
-                v[e] = ((mk[c] >> e) & 1u) ? 0.f : __uint_as_float(r[e]) * p.scale_log2;
+                v[e] = ((mk[c] >> e) & 1u) ? 0.f : __uint_as_float(r[c * 32 + e]) * p.scale_log2;
             } else if (mk[c] == 0u) {
 #pragma unroll
-              for (int e = 0; e < 32; ++e) v[e] = ex2_approx(fmaf(__uint_as_float(r[e]), p.scale_log2, neg_m));
+              for (int e = 0; e < 32; ++e)
+                v[e] = ex2_approx(fmaf(__uint_as_float(r[c * 32 + e]), p.scale_log2, neg_m));
             } else {
 #pragma unroll
               for (int e = 0; e < 32; ++e)
-                v[e] = ((mk[c] >> e) & 1u) ? 0.f : ex2_approx(fmaf(__uint_as_float(r[e]), p.scale_log2, neg_m));
+                v[e] = ((mk[c] >> e) & 1u) ? 0.f
+                                           : ex2_approx(fmaf(__uint_as_float(r[c * 32 + e]), p.scale_log2, neg_m));
             }
 #pragma unroll
             for (int e = 0; e < 32; e += 4) {
@@ -431,7 +486,6 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_fwd_kernel(const __grid_co
               l2 += v[e + 2];
               l3 += v[e + 3];
             }
-            const uint32_t base = sPw + (c >> 1) * kAtTile + row_in * 128;
 #pragma unroll
             for (int jv = 0; jv < 4; ++jv) {
               uint4 qv;
@@ -439,42 +493,57 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_fwd_kernel(const __grid_co
               qv.y = pack2<T>(v[8 * jv + 2], v[8 * jv + 3]);
               qv.z = pack2<T>(v[8 * jv + 4], v[8 * jv + 5]);
               qv.w = pack2<T>(v[8 * jv + 6], v[8 * jv + 7]);
-              st_shared_v4(base + ((((c & 1) * 4 + jv) ^ sw) * 16), qv);
+              st_shared_v4(sPh + (((c * 4 + jv) ^ sw) * 16), qv);
             }
           }
           l += (l0 + l1) + (l2 + l3);
-          tc_fence_before();           // our TMEM reads (S) and writes (O) precede the MMAs released below
+          tc_fence_before();           // a rescale of O_st (TMEM stores) precedes the MMA released below
           fence_proxy_async_smem();    // P (generic-proxy stores) -> tensor core (async proxy)
           __syncwarp();
-          if (lane == 0) {
-            mbar_arrive(&s_empty[w]);
-            mbar_arrive(&p_full[w]);
-          }
+          if (lane == 0) mbar_arrive(&p_full[st]);
         }
       }
-      // ---- row block finished: O = acc / l
-      mbar_wait(&o_done[w], od_ph, 19);
+      // ---- row block finished: merge the two column-half streams of every row, O = (Oa fa + Ob fb) / l
+      mbar_wait(&o_done[st], od_ph, 19);
       od_ph ^= 1;
       tc_fence_after();
-      const float inv = raw ? 1.f : 1.f / l;  // l == 0 (fully masked row): inf -> NaN row, as in the reference
-      const uint32_t sbuf = sPw + q * 4096;   // this warp's own 32 rows of P k-chunk 0 double as staging tile
-#pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        uint32_t r[32];
-        tmem_ld_32x32(tO + h * 32, r);
+      sStat[(w * 2 + h) * kAtBM + row_in] = make_float2(m_used, l);
+      tc_fence_before();
+      named_bar_sync(pair_bar, 64);  // partner's statistics written; both streams' last MMAs have finished
+      tc_fence_after();
+      const float2 other = sStat[(w * 2 + (h ^ 1)) * kAtBM + row_in];
+      const float m_all = fmaxf(m_used, other.x);
+      float f_own = 1.f, f_oth = 1.f;
+      if (!kRaw) {
+        f_own = (m_used == -INFINITY) ? 0.f : ex2_approx(m_used - m_all);
+        f_oth = (other.x == -INFINITY) ? 0.f : ex2_approx(other.x - m_all);
+      }
+      const float l_all = l * f_own + other.y * f_oth;
+      const float inv = kRaw ? 1.f : 1.f / l_all;  // l == 0 (fully masked row): inf -> NaN row, as in the reference
+      const float fa = (h == 0 ? f_own : f_oth) * inv, fb = (h == 0 ? f_oth : f_own) * inv;
+      // this thread produces output columns [h*32, h*32+32) of its row from both accumulators
+      const uint32_t sbuf = sPw + q * 4096;  // 32 rows of P k-chunk 0 double as the staging tile of (w, q)
+      {
+        uint32_t ra[32], rb[32];
+        tmem_ld_32x32(lane_base + 2 * kAtBN + (w * 2) * 64 + h * 32, ra);
+        tmem_ld_32x32(lane_base + 2 * kAtBN + (w * 2 + 1) * 64 + h * 32, rb);
         tmem_ld_wait();
-        tmem_ld_pin(r);
+        tmem_ld_pin(ra);
+        tmem_ld_pin(rb);
         float v[32];
 #pragma unroll
-        for (int e = 0; e < 32; ++e) v[e] = __uint_as_float(r[e]) * inv;
+        for (int e = 0; e < 32; ++e) {
+          // 0 * inf = NaN marks a fully masked row; a dead stream (factor 0, accumulator 0) contributes 0 * inv
+          v[e] = __uint_as_float(ra[e]) * fa + __uint_as_float(rb[e]) * fb;
+        }
         stage_row32<T>(sbuf, lane, v, h);
       }
       tc_fence_before();
+      fence_proxy_async_smem();
+      named_bar_sync(pair_bar, 64);  // both halves of the staging tile are written
       const int rows_valid = max(0, min(32, p.M - row0));
-      if (rows_valid > 0) {
+      if (h == 0 && rows_valid > 0) {
         if (p.o_tma_ok) {
-          fence_proxy_async_smem();
-          __syncwarp();
           if (lane == 0) {
             tma_store_5d(&p.tmO, sbuf, 0, 0, row0, b0i, b1i);
             bulk_commit_group();
@@ -482,13 +551,15 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_fwd_kernel(const __grid_co
           }
           __syncwarp();
         } else {
-          __syncwarp();
           T* dst = reinterpret_cast<T*>(p.O) + b1i * p.o_sb1 + b0i * p.o_sb0 + static_cast<long long>(row0) * p.ldo;
           store_rows_generic<T>(sbuf, dst, p.ldo, rows_valid, p.dv, p.o_vec_ok != 0, lane);
           __syncwarp();
         }
-        if (p.lse != nullptr && row < p.M) p.lse[static_cast<size_t>(b) * p.M + row] = m_used + log2f(l);
+        if (p.lse != nullptr && row < p.M) p.lse[static_cast<size_t>(b) * p.M + row] = m_all + log2f(l_all);
       }
+      // the partner must not overwrite the staging rows (its own P rows live in k-chunk 1, but the NEXT staging
+      // pass writes k-chunk 0 again) before the store above has read them
+      named_bar_sync(pair_bar, 64);
     }
   }
 
