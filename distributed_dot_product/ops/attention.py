@@ -88,6 +88,65 @@ def fused_softmax_nt(k4, q4, mask, scale, offset):
     return probs
 
 
+#: run the no-grad forward through the slab-free attention kernel (``ddp_attn_fwd``) when the shapes allow it
+FLASH_FWD = bool(int(__import__('os').environ.get('DDP_FLASH_FWD', '1')))
+
+
+def flash_eligible(k4, q4, v4, mask, world):
+    """True if ``ddp_attn_fwd`` covers these ``[B, H, rows, d]`` operands (16-bit, head dims <= 64, zero-copy
+    views); everything else takes the three-kernel path."""
+    if k4.dtype not in (torch.bfloat16, torch.float16) or q4.dtype != k4.dtype or v4.dtype != k4.dtype:
+        return False
+    d, dv = k4.size(-1), v4.size(-1)
+    if d != q4.size(-1) or d % 8 or dv % 8 or not 8 <= d <= 64 or not 8 <= dv <= 64:
+        return False
+    if q4.size(-2) != v4.size(-2) or k4.dim() != 4:
+        return False
+    if mask is not None and (mask.dtype != torch.bool or (world > 1 and q4.size(-2) % 32)):
+        return False
+    return all(_g._aligned(t) for t in (k4, q4, v4))
+
+
+def flash_attention_forward(k4, q4, v4, mask, scale, offset, out4, want_lse=False):
+    """``out4 = softmax(scale * k4 @ gather(q4)^T masked) @ gather(v4)`` in ONE kernel (reference:
+    module.py:61-69): scores stay in TMEM, probabilities go through shared memory back into the tensor
+    core, the ``[T/N, T]`` slab is never written; the all-gather of ``q4`` / ``v4`` is fused in.
+    Returns the fp32 row log-sum-exp (log2 domain) if ``want_lse``."""
+    import ctypes
+    from distributed_dot_product.ops.softmax import _prep_mask
+    from distributed_dot_product.parallel import runtime
+    lib = _native.load()
+    world = runtime.get_world_size()
+    b, h, tn, _ = k4.shape
+    total = world * q4.size(-2)
+    bits, ldw, sb1w = None, 0, 0
+    if mask is not None:
+        mu8, m_ld, m_sb1 = _prep_mask(mask, torch.empty((b, h, tn, total), device='meta'))
+        ldw = (total + 31) // 32
+        bits = torch.empty(b, tn, ldw, dtype=torch.int32, device=k4.device)
+        _native.check(lib.ddp_pack_mask(ctypes.c_void_p(mu8.data_ptr()), b, tn, total, m_ld, m_sb1,
+                                        ctypes.c_void_p(bits.data_ptr()), ldw, _g._stream()))
+        _native.count_launch()
+        sb1w = tn * ldw
+    lse = torch.empty(b, h, tn, dtype=torch.float32, device=k4.device) if want_lse else None
+    va, vb, vv, vo = _g.as_view(k4), _g.as_view(q4), _g.as_view(v4), _g.as_view(out4)
+    comm_ptr = None
+    if world > 1:
+        chunk = _g.chunk_rows_from_offset(offset, q4.size(-2), 2 * b * h)
+        ws, nf = ctypes.c_size_t(), ctypes.c_size_t()
+        _native.check(lib.ddp_attn_fwd_workspace(ctypes.byref(vb), ctypes.byref(vv), world, chunk,
+                                                 ctypes.byref(ws), ctypes.byref(nf)))
+        hp = runtime.heap()
+        hp.ensure(ws.value, nf.value)
+        comm_ptr = ctypes.byref(hp.next_comm(chunk))
+    _native.check(lib.ddp_attn_fwd(ctypes.byref(va), ctypes.byref(vb), ctypes.byref(vv), ctypes.byref(vo),
+                                   ctypes.c_void_p(lse.data_ptr()) if lse is not None else None,
+                                   ctypes.c_void_p(bits.data_ptr()) if bits is not None else None, ldw, sb1w,
+                                   float(scale), comm_ptr, 0, _g._stream()))
+    _native.count_launch()
+    return lse
+
+
 def _rowdot(a, b):
     """fp32 ``(a * b).sum(-1)`` of two 2-D CUDA tensors (``ddp_rowdot``)."""
     import ctypes
@@ -155,5 +214,16 @@ class _AttentionCore(torch.autograd.Function):
 
 
 def attention_core(keys, queries, values, mask, num_heads, scale, offset=32):
-    """``softmax(scale * K Q^T masked) V`` with K/Q/V given as ``[B, T/N, H*d]`` projections."""
+    """``softmax(scale * K Q^T masked) V`` with K/Q/V given as ``[B, T/N, H*d]`` projections.
+
+    When no gradient is required (inference) and the shapes allow it, the whole thing is ONE slab-free
+    kernel (``flash_attention_forward``); the training path keeps the probability slab for its backward."""
+    needs_grad = torch.is_grad_enabled() and any(t.requires_grad for t in (keys, queries, values))
+    if FLASH_FWD and not needs_grad and scale > 0:
+        from distributed_dot_product.parallel import runtime
+        k4, q4, v4 = _heads(keys, num_heads), _heads(queries, num_heads), _heads(values, num_heads)
+        if flash_eligible(k4, q4, v4, mask, runtime.get_world_size()):
+            out = torch.empty(keys.shape[:-1] + (values.size(-1),), dtype=values.dtype, device=values.device)
+            flash_attention_forward(k4, q4, v4, mask, scale, offset, _heads(out, num_heads))
+            return out
     return _AttentionCore.apply(keys, queries, values, mask, num_heads, scale, offset)

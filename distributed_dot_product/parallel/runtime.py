@@ -225,10 +225,10 @@ def check_status():
         return 0
     lib = _native.load()
     torch.cuda.synchronize()
-    site = max(lib.ddp_debug_timeout_site(), lib.ddp_debug_timeout_site_rowops())
+    site = max(lib.ddp_debug_timeout_site(), lib.ddp_debug_timeout_site_rowops(), lib.ddp_debug_timeout_site_attn())
     if site > 0:
         raise RuntimeError('distributed-dot-product: an in-kernel pipeline wait gave up after 4 s (site %d: '
-                           '1 smem slot, 2 TMEM buffer, 3 operands, 4 accumulator, 5 P chunk, 6 softmax row); results are '
+                           '1 smem slot, 2 TMEM buffer, 3 operands, 4 accumulator, 5 P chunk, 6 softmax row, 11-19 attention forward); results are '
                            'invalid - please report this shape' % site)
     hp = _Heap._instance
     if hp is None or hp.base is None:

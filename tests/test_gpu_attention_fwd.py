@@ -1,0 +1,103 @@
+# -*- coding: utf-8 -*-
+"""Slab-free attention forward (``ddp_attn_fwd``) against a plain PyTorch fp32 reference (one GPU).
+
+Reference semantics: module.py:61-69 (scale, masked_fill(-inf), softmax over the gathered axis, attn @ V).
+"""
+import math
+import os
+import subprocess
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _reference(k, q, v, mask, heads, scale):
+    b, tn, hd = k.shape
+    d = hd // heads
+    k4 = k.float().view(b, tn, heads, d).transpose(1, 2)
+    q4 = q.float().view(b, q.size(1), heads, d).transpose(1, 2)
+    v4 = v.float().view(b, v.size(1), heads, -1).transpose(1, 2)
+    s = (k4 @ q4.transpose(-1, -2)) * scale
+    if mask is not None:
+        s = s.masked_fill(mask.unsqueeze(1), float('-inf'))
+    p = torch.softmax(s, dim=-1)
+    return (p @ v4).transpose(1, 2).reshape(b, tn, -1)
+
+
+@pytest.mark.parametrize('dtype', [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize('b,heads,tn,t,d,masked', [
+    (1, 1, 256, 256, 64, False),
+    (2, 4, 300, 300, 32, True),     # ragged rows / columns, random mask
+    (1, 16, 512, 1024, 64, True),   # the flagship head shape, more columns than rows
+    (1, 2, 100, 72, 40, True),      # head dim not a power of two
+])
+def test_flash_forward_matches_reference(cuda_device, dtype, b, heads, tn, t, d, masked):
+    from distributed_dot_product.ops.attention import flash_attention_forward, flash_eligible, _heads
+    torch.manual_seed(1)
+    k = torch.randn(b, tn, heads * d, device=cuda_device).to(dtype)
+    q = torch.randn(b, t, heads * d, device=cuda_device).to(dtype)
+    v = torch.randn(b, t, heads * d, device=cuda_device).to(dtype)
+    mask = None
+    if masked:
+        mask = torch.rand(b, tn, t, device=cuda_device) < 0.3
+        mask[:, 3, :] = True          # a fully masked row -> NaN, as softmax over -inf in the reference
+        mask[:, 5, : t - 1] = True    # a single live column
+    scale = 1.0 / math.sqrt(d)
+    k4, q4, v4 = _heads(k, heads), _heads(q, heads), _heads(v, heads)
+    assert flash_eligible(k4, q4, v4, mask, 1)
+    out = torch.empty(b, tn, heads * d, device=cuda_device, dtype=dtype)
+    lse = flash_attention_forward(k4, q4, v4, mask, scale, 64, _heads(out, heads), want_lse=True)
+    ref = _reference(k, q, v, mask, heads, scale)
+    got = out.float()
+    if masked:
+        assert torch.isnan(got[:, 3]).all() and torch.isnan(ref[:, 3]).all()
+        got = got.clone()
+        ref = ref.clone()
+        got[:, 3] = 0
+        ref[:, 3] = 0
+    err = (got - ref).abs().max().item()
+    assert err <= 2e-2 * max(1.0, ref.abs().max().item()), err
+    # log-sum-exp (log2 domain) of the scaled, masked scores
+    s = (_heads(k, heads).float() @ _heads(q, heads).float().transpose(-1, -2)) * scale
+    if mask is not None:
+        s = s.masked_fill(mask.unsqueeze(1), float('-inf'))
+    lse_ref = torch.logsumexp(s, dim=-1) * math.log2(math.e)
+    ok = torch.isfinite(lse_ref)
+    assert (lse[ok] - lse_ref[ok]).abs().max().item() <= 2e-2
+
+
+def test_module_inference_uses_flash_and_matches_training_path(cuda_device):
+    """``DistributedDotProductAttn`` under ``torch.no_grad()`` runs the slab-free kernel; its output must agree
+    with the training path (three kernels, probability slab kept) and with the dense twin."""
+    from distributed_dot_product import _native
+    from distributed_dot_product.module import DistributedDotProductAttn
+    torch.manual_seed(2)
+    m = DistributedDotProductAttn(256, num_heads=4, add_bias=True, offset=64).to(cuda_device).to(torch.bfloat16)
+    x = torch.randn(2, 384, 256, device=cuda_device, dtype=torch.bfloat16)
+    mask = torch.rand(2, 384, 384, device=cuda_device) < 0.2
+    xg = x.clone().requires_grad_(True)
+    train_out = m(xg, xg, xg, mask)
+    before = _native.launch_count
+    with torch.no_grad():
+        infer_out = m(x, x, x, mask)
+    launches = _native.launch_count - before
+    # 4 projections + mask packing + ONE attention kernel (the training path needs 3 kernels for the core)
+    assert launches == 6, launches
+    err = (infer_out.float() - train_out.float()).abs().max().item()
+    assert err <= 3e-2 * max(1.0, train_out.float().abs().max().item()), err
+
+
+def test_attention_harness_emulated_ranks(cuda_device):
+    """The standalone CUDA harness validates the fused all-gather of the attention kernel with emulated ranks on
+    one GPU (produce phase of every rank, then consume phase) - see csrc/tests/attn_harness.cu."""
+    exe = os.path.join(ROOT, 'build', 'attn_harness')
+    if not os.path.exists(exe):
+        subprocess.check_call(['python', os.path.join(ROOT, 'build.py'), 'harness'], cwd=ROOT)
+    r = subprocess.run([exe, 'quick'], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
+    tail = '\n'.join(r.stdout.splitlines()[-20:])
+    assert r.returncode == 0, tail
+    assert 'fail=0' in r.stdout, tail
