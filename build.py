@@ -31,6 +31,7 @@ HEADERS = [
     "csrc/gemm/gemm_sm100.cuh",
     "csrc/gemm/tma_map.h",
     "csrc/attn/attn_fwd_sm100.cuh",
+    "csrc/attn/attn_bwd_sm100.cuh",
 ]
 LIB_OUT = "distributed_dot_product/_lib/libddp_b200.so"
 

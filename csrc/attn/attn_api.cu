@@ -7,7 +7,7 @@
 
 #include "../common/host_util.h"
 #include "../gemm/tma_map.h"
-#include "attn_fwd_sm100.cuh"
+#include "attn_bwd_sm100.cuh"
 
 namespace ddp {
 
@@ -168,4 +168,265 @@ extern "C" int ddp_attn_fwd(const ddp_tensor* A, const ddp_tensor* B, const ddp_
   int grid = world > 1 ? sms : (int)(items < sms ? items : sms);
   if (grid < 1) grid = 1;
   return dt == DDP_BF16 ? attn_launch<DDP_BF16>(p, grid, stream) : attn_launch<DDP_F16>(p, grid, stream);
+}
+
+// ---------------------------------------------------------------------------------------------- backward
+namespace ddp {
+
+constexpr int kAbRowsStages = 6;
+constexpr int kAbRowsSmem = 6 * kAtTile + kAbRowsStages * 2 * kAbHalfTile + (2 * kAbRowsStages + 10) * 8 + 16 + 1024;
+static_assert(kAbRowsSmem <= 232448, "shared memory budget exceeded");
+
+template <typename Kern>
+static int attn_bwd_launch(Kern kern, bool* configured, int smem, const AttnBwdParams& p, int grid, cudaStream_t stream) {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 64 && !configured[dev]) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return set_error(-12, cudaGetErrorString(e));
+    configured[dev] = true;
+  }
+  kern<<<grid, kAtThreads, smem, stream>>>(p);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return set_error(-13, cudaGetErrorString(e));
+  return 0;
+}
+
+// Fills the collective part of the parameters (gather of B and V) - shared by both backward kernels.
+static int attn_bwd_comm(AttnBwdParams& p, const ddp_tensor* B, const ddp_tensor* V, const ddp_comm* comm,
+                         uint32_t box_rows) {
+  const int world = p.world, rank = p.rank;
+  const uint64_t Bt = (uint64_t)B->b0 * B->b1;
+  int chunk_rows = comm->chunk_rows < 1 ? 1 : comm->chunk_rows;
+  const ddp_tensor* src[2] = {B, V};
+  p.ws_v_off = (long long)(((size_t)world * Bt * B->rows * B->cols * 2 + 1023) & ~(size_t)1023);
+  for (int i = 0; i < 2; ++i) {
+    const ddp_tensor* t = src[i];
+    const uint64_t row_bytes = (uint64_t)t->cols * 2;
+    if (reinterpret_cast<uintptr_t>(t->ptr) & 15 || (t->ld * 2) % 16 || (t->sb0 * 2) % 16 || (t->sb1 * 2) % 16)
+      return set_error(-2, "attn: gathered operand is not 16-byte aligned");
+    uint64_t gd[5] = {(uint64_t)t->cols, 1, (uint64_t)t->rows, Bt, (uint64_t)world};
+    uint64_t gs[4] = {row_bytes, row_bytes, row_bytes * t->rows, row_bytes * t->rows * Bt};
+    uint32_t box[5] = {64, 1, box_rows, 1, 1};
+    char* base = static_cast<char*>(comm->ws[rank]) + (i ? p.ws_v_off : 0);
+    if (int e = make_map(i ? &p.tmVg : &p.tmBg, t->dtype, base, gd, gs, box, false)) return e;
+    p.push_src[i] = static_cast<const char*>(t->ptr);
+    p.push_ld[i] = t->ld * 2; p.push_sb0[i] = t->sb0 * 2; p.push_sb1[i] = t->sb1 * 2;
+    p.push_row_bytes[i] = (int)row_bytes;
+  }
+  p.push_rows = (int)B->rows;
+  p.seq = comm->seq; p.phase_mask = comm->phase_mask;
+  p.chunk_rows = chunk_rows;
+  p.n_chunks = (int)((B->rows + chunk_rows - 1) / chunk_rows);
+  for (int i = 0; i < world; ++i) {
+    p.ws[i] = static_cast<char*>(comm->ws[i]);
+    p.flags[i] = comm->flags[i];
+    p.done[i] = comm->done[i];
+  }
+  p.exit_counter = comm->exit_counter;
+  p.status = comm->status;
+  return 0;
+}
+
+static bool out_vec_ok(const ddp_tensor* O) {
+  return ((reinterpret_cast<uintptr_t>(O->ptr) & 15) == 0) && ((O->ld * 2) % 16 == 0) && ((O->sb0 * 2) % 16 == 0) &&
+         ((O->sb1 * 2) % 16 == 0);
+}
+
+}  // namespace ddp
+
+extern "C" int ddp_attn_bwd_rows(const ddp_tensor* A, const ddp_tensor* G, const ddp_tensor* B, const ddp_tensor* V,
+                                 const ddp_tensor* dA, const float* neg_lse, const float* nds, int64_t stat_ld,
+                                 const uint32_t* mask_bits, int64_t mask_ld_words, int64_t mask_sb1_words, float scale,
+                                 const ddp_comm* comm, int dbg, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  const int world = comm ? comm->world : 1;
+  const int rank = comm ? comm->rank : 0;
+  if (int e = attn_check(A, B, V, world)) return e;
+  if (!G || !dA || !neg_lse || !nds) return set_error(-4, "attn bwd: dO, dA, neg_lse and nds are required");
+  const int dt = A->dtype;
+  if (G->dtype != dt || G->rows != A->rows || G->cols != V->cols || G->b0 != A->b0 || G->b1 != A->b1)
+    return set_error(-4, "attn bwd: dO has the wrong shape or dtype");
+  if (dA->dtype != dt || dA->rows != A->rows || dA->cols != A->cols || dA->b0 != A->b0 || dA->b1 != A->b1)
+    return set_error(-4, "attn bwd: dA has the wrong shape or dtype");
+  if (!(scale > 0.f)) return set_error(-4, "attn: scale must be positive");
+  if (stat_ld < A->rows) return set_error(-4, "attn bwd: stat_ld < rows");
+  if (mask_bits && world > 1 && (B->rows % 32)) return set_error(-6, "attn: masked, world > 1: T/N must be a multiple of 32");
+
+  AttnBwdParams p;
+  memset(&p, 0, sizeof p);
+  p.M = (int)A->rows; p.Tn = (int)B->rows; p.d = (int)A->cols; p.dv = (int)V->cols;
+  p.b0 = (int)A->b0; p.b1 = (int)A->b1;
+  p.world = world; p.rank = rank;
+  const int m_blocks = (p.M + kAtBM - 1) / kAtBM;
+  p.m_pairs = (m_blocks + 1) / 2;
+  p.n_steps = (p.Tn + kAbStep - 1) / kAbStep;
+  p.out0 = dA->ptr; p.ld0 = dA->ld; p.o0_sb0 = dA->sb0; p.o0_sb1 = dA->sb1;
+  p.neg_lse = neg_lse; p.nds = nds; p.stat_ld = stat_ld;
+  p.mask_bits = mask_bits; p.mb_ld = mask_ld_words; p.mb_sb1 = mask_sb1_words;
+  p.scale = scale; p.scale_log2 = scale * 1.4426950408889634f;
+  p.dbg = dbg;
+  if (int e = tile_map(&p.tmA, A, kAtBM, false)) return e;
+  if (int e = tile_map(&p.tmG, G, kAtBM, false)) return e;
+  if (int e = tile_map(&p.tmB, B, kAbStep, false)) return e;
+  if (int e = tile_map(&p.tmV, V, kAbStep, false)) return e;
+  p.o0_vec_ok = out_vec_ok(dA);
+  if (p.o0_vec_ok && !(dbg & 16) && tile_map(&p.tmOut0, dA, 32, false) == 0) p.o0_tma_ok = 1;
+  if (!p.o0_tma_ok) p.tmOut0 = p.tmA;
+  p.tmOut1 = p.tmA;
+  p.tmBg = p.tmB;
+  p.tmVg = p.tmV;
+  if (world > 1) {
+    if (int e = attn_bwd_comm(p, B, V, comm, kAbStep)) return e;
+  } else {
+    p.phase_mask = 3; p.chunk_rows = 1 << 30; p.n_chunks = 1;
+  }
+  const long long items = (long long)p.b1 * p.m_pairs * p.b0;
+  const int sms = ddp_num_sms();
+  int grid = world > 1 ? sms : (int)(items < sms ? items : sms);
+  if (grid < 1) grid = 1;
+  static bool cfg_bf[64] = {}, cfg_h[64] = {};
+  return dt == DDP_BF16
+             ? attn_bwd_launch(attn_bwd_rows_kernel<DDP_BF16, kAbRowsStages>, cfg_bf, kAbRowsSmem, p, grid, stream)
+             : attn_bwd_launch(attn_bwd_rows_kernel<DDP_F16, kAbRowsStages>, cfg_h, kAbRowsSmem, p, grid, stream);
+}
+
+// ---------------------------------------------------------------------------------------------- column side
+namespace ddp {
+
+constexpr int kAbColsStages = 5;
+constexpr int kAbColsSmem = 8 * kAtTile + kAbColsStages * kAbColsStage + (2 * kAbColsStages + 10) * 8 + 16 + 1024;
+static_assert(kAbColsSmem <= 232448, "shared memory budget exceeded");
+
+struct ColsLayout {
+  size_t v_off, p0_off, p1_off, bytes, gather_flags, flags;
+};
+static ColsLayout cols_layout(const ddp_tensor* B, const ddp_tensor* V, int world, int chunk_rows) {
+  ColsLayout L;
+  const size_t Bt = (size_t)B->b0 * B->b1;
+  const size_t al = 1023;
+  if (chunk_rows < 1) chunk_rows = 1;
+  const size_t n_chunks = ((size_t)B->rows + chunk_rows - 1) / chunk_rows;
+  const size_t n_mb = ((size_t)B->rows + kAtBM - 1) / kAtBM;
+  L.v_off = ((size_t)world * Bt * B->rows * B->cols * 2 + al) & ~al;
+  L.p0_off = (L.v_off + (size_t)world * Bt * V->rows * V->cols * 2 + al) & ~al;
+  L.p1_off = (L.p0_off + (size_t)world * Bt * V->rows * V->cols * 4 + al) & ~al;
+  L.bytes = L.p1_off + (size_t)world * Bt * B->rows * B->cols * 4;
+  L.gather_flags = 2 * (size_t)world * Bt * n_chunks;
+  L.flags = L.gather_flags + (size_t)world * Bt * n_mb * 8;
+  return L;
+}
+
+// bits_t[b1][cols][ld_words]: bit (r & 31) of word r >> 5 <- mask[b1][r][col] != 0; bits past `rows` are set.
+__global__ void pack_mask_t_kernel(const uint8_t* __restrict__ mask, long long b1, long long rows, long long cols,
+                                   long long m_ld, long long m_sb1, uint32_t* __restrict__ bits, long long ld_words) {
+  const long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const long long per_b = ld_words * cols;
+  if (idx >= b1 * per_b) return;
+  const long long b1i = idx / per_b;
+  const long long r = idx - b1i * per_b;
+  const long long w = r / cols, col = r - w * cols;  // adjacent threads -> adjacent columns (coalesced reads)
+  const uint8_t* src = mask + b1i * m_sb1 + col;
+  uint32_t word = 0;
+  for (int k = 0; k < 32; ++k) {
+    const long long row = w * 32 + k;
+    if (row >= rows || src[row * m_ld] != 0) word |= 1u << k;
+  }
+  bits[(b1i * cols + col) * ld_words + w] = word;
+}
+
+}  // namespace ddp
+
+extern "C" int ddp_pack_mask_t(const uint8_t* mask, int64_t b1, int64_t rows, int64_t cols, int64_t mask_ld,
+                               int64_t mask_sb1, uint32_t* bits_t, int64_t ld_words, void* stream) {
+  const long long total = b1 * cols * ld_words;
+  if (total <= 0) return 0;
+  const int threads = 256;
+  const long long blocks = (total + threads - 1) / threads;
+  ddp::pack_mask_t_kernel<<<static_cast<unsigned>(blocks), threads, 0, static_cast<cudaStream_t>(stream)>>>(
+      mask, b1, rows, cols, mask_ld, mask_sb1, bits_t, ld_words);
+  return ddp::cuda_check(cudaGetLastError(), "pack_mask_t launch");
+}
+
+extern "C" int ddp_attn_bwd_cols_workspace(const ddp_tensor* B, const ddp_tensor* V, int world, int chunk_rows,
+                                           size_t* ws_bytes, size_t* n_flags) {
+  if (!B || !V) return set_error(-4, "attn: B and V are required");
+  if (world <= 1) {
+    *ws_bytes = 0;
+    *n_flags = 0;
+    return 0;
+  }
+  const ColsLayout L = cols_layout(B, V, world, chunk_rows);
+  *ws_bytes = L.bytes;
+  *n_flags = L.flags;
+  return 0;
+}
+
+extern "C" int ddp_attn_bwd_cols(const ddp_tensor* A, const ddp_tensor* G, const ddp_tensor* B, const ddp_tensor* V,
+                                 const ddp_tensor* dV, const ddp_tensor* dB, const float* neg_lse, const float* nds,
+                                 int64_t stat_ld, const uint32_t* mask_bits_t, int64_t mask_ld_words,
+                                 int64_t mask_sb1_words, float scale, const ddp_comm* comm, int dbg, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  const int world = comm ? comm->world : 1;
+  const int rank = comm ? comm->rank : 0;
+  if (int e = attn_check(A, B, V, world)) return e;
+  if (!G || !dV || !dB || !neg_lse || !nds) return set_error(-4, "attn bwd: dO, dV, dB, neg_lse and nds are required");
+  const int dt = A->dtype;
+  if (G->dtype != dt || G->rows != A->rows || G->cols != V->cols || G->b0 != A->b0 || G->b1 != A->b1)
+    return set_error(-4, "attn bwd: dO has the wrong shape or dtype");
+  if (dV->dtype != dt || dV->rows != V->rows || dV->cols != V->cols || dV->b0 != A->b0 || dV->b1 != A->b1)
+    return set_error(-4, "attn bwd: dV has the wrong shape or dtype");
+  if (dB->dtype != dt || dB->rows != B->rows || dB->cols != B->cols || dB->b0 != A->b0 || dB->b1 != A->b1)
+    return set_error(-4, "attn bwd: dB has the wrong shape or dtype");
+  if (!(scale > 0.f)) return set_error(-4, "attn: scale must be positive");
+  if (stat_ld < A->rows || stat_ld % 64) return set_error(-4, "attn bwd: stat_ld must be a multiple of 64 >= rows");
+  if (reinterpret_cast<uintptr_t>(neg_lse) & 15 || reinterpret_cast<uintptr_t>(nds) & 15)
+    return set_error(-2, "attn bwd: the row statistics must be 16-byte aligned");
+
+  AttnBwdParams p;
+  memset(&p, 0, sizeof p);
+  p.M = (int)A->rows; p.Tn = (int)B->rows; p.d = (int)A->cols; p.dv = (int)V->cols;
+  p.b0 = (int)A->b0; p.b1 = (int)A->b1;
+  p.world = world; p.rank = rank;
+  const int n_mb = (p.Tn + kAtBM - 1) / kAtBM;
+  p.m_pairs = (n_mb + 1) / 2;
+  p.n_steps = (p.M + kAbStep - 1) / kAbStep;
+  p.out0 = dV->ptr; p.ld0 = dV->ld; p.o0_sb0 = dV->sb0; p.o0_sb1 = dV->sb1;
+  p.out1 = dB->ptr; p.ld1 = dB->ld; p.o1_sb0 = dB->sb0; p.o1_sb1 = dB->sb1;
+  p.neg_lse = neg_lse; p.nds = nds; p.stat_ld = stat_ld;
+  p.mask_bits = mask_bits_t; p.mb_ld = mask_ld_words; p.mb_sb1 = mask_sb1_words;
+  p.scale = scale; p.scale_log2 = scale * 1.4426950408889634f;
+  p.dbg = dbg;
+  if (int e = tile_map(&p.tmA, A, kAbStep, false)) return e;
+  if (int e = tile_map(&p.tmG, G, kAbStep, false)) return e;
+  if (int e = tile_map(&p.tmB, B, kAtBM, false)) return e;
+  if (int e = tile_map(&p.tmV, V, kAtBM, false)) return e;
+  p.o0_vec_ok = out_vec_ok(dV);
+  p.o1_vec_ok = out_vec_ok(dB);
+  if (world > 1 && !(p.o0_vec_ok && p.o1_vec_ok)) return set_error(-6, "attn bwd: world > 1 needs 16-byte aligned outputs");
+  if (p.o0_vec_ok && !(dbg & 16) && tile_map(&p.tmOut0, dV, 32, false) == 0) p.o0_tma_ok = 1;
+  if (p.o1_vec_ok && !(dbg & 16) && tile_map(&p.tmOut1, dB, 32, false) == 0) p.o1_tma_ok = 1;
+  if (!p.o0_tma_ok) p.tmOut0 = p.tmA;
+  if (!p.o1_tma_ok) p.tmOut1 = p.tmA;
+  p.tmBg = p.tmB;
+  p.tmVg = p.tmV;
+  if (world > 1) {
+    if (int e = attn_bwd_comm(p, B, V, comm, kAtBM)) return e;
+    const ColsLayout L = cols_layout(B, V, world, p.chunk_rows);
+    if ((size_t)p.ws_v_off != L.v_off) return set_error(-20, "attn bwd: workspace layout mismatch");
+    p.ws_p0_off = (long long)L.p0_off;
+    p.ws_p1_off = (long long)L.p1_off;
+    p.rs_flag_off = (long long)L.gather_flags;
+    if (p.phase_mask == 3) p.phase_mask = 7;  // production: push, main loop and reduction in one launch
+  } else {
+    p.phase_mask = 7; p.chunk_rows = 1 << 30; p.n_chunks = 1;
+  }
+  const long long items = (long long)world * p.b1 * p.m_pairs * p.b0;
+  const int sms = ddp_num_sms();
+  int grid = world > 1 ? sms : (int)(items < sms ? items : sms);
+  if (grid < 1) grid = 1;
+  static bool cfg_bf[64] = {}, cfg_h[64] = {};
+  return dt == DDP_BF16
+             ? attn_bwd_launch(attn_bwd_cols_kernel<DDP_BF16, kAbColsStages>, cfg_bf, kAbColsSmem, p, grid, stream)
+             : attn_bwd_launch(attn_bwd_cols_kernel<DDP_F16, kAbColsStages>, cfg_h, kAbColsSmem, p, grid, stream);
 }

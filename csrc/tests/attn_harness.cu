@@ -292,6 +292,280 @@ static bool run_case(const Case& c, int dbg, bool verbose) {
   return ok;
 }
 
+
+// ---------------------------------------------------------------------------------------------- backward
+// Validates ddp_attn_bwd_rows / ddp_attn_bwd_cols against a double-precision reference.  The row statistics
+// (-L, -scale*delta) come from the CPU reference, so the two kernels are tested independently of the forward.
+static bool run_bwd_case(const Case& c, bool verbose) {
+  const int W = c.world, T = W * c.Tn;
+  const float scale = 1.0f / sqrtf((float)c.d);
+  const double sl2 = (double)scale * 1.4426950408889634;
+  const int Bt = c.b1 * c.b0;
+  const long long stat_ld = (c.M + 63) / 64 * 64;
+  std::vector<HT> A(W), B(W), V(W), G(W), dA(W), dB(W), dV(W);
+  std::vector<std::vector<uint8_t>> mask(W);
+  for (int r = 0; r < W; ++r) {
+    A[r] = make_ht(c.b1, c.b0, c.M, c.d, c.interleave, true);
+    B[r] = make_ht(c.b1, c.b0, c.Tn, c.d, c.interleave, true);
+    V[r] = make_ht(c.b1, c.b0, c.Tn, c.dv, c.interleave, true);
+    G[r] = make_ht(c.b1, c.b0, c.M, c.dv, c.interleave, true);
+    dA[r] = make_ht(c.b1, c.b0, c.M, c.d, c.interleave, false);
+    dB[r] = make_ht(c.b1, c.b0, c.Tn, c.d, c.interleave, false);
+    dV[r] = make_ht(c.b1, c.b0, c.Tn, c.dv, c.interleave, false);
+    if (c.maskmode) {
+      mask[r].assign((size_t)c.b1 * c.M * T, 0);
+      for (int i1 = 0; i1 < c.b1; ++i1)
+        for (int m = 0; m < c.M; ++m)
+          for (int t = 0; t < T; ++t) {
+            uint8_t v = 0;
+            if (c.maskmode == 1) v = irand(0, 9) < 3;
+            if (c.maskmode == 2) v = (m % 37 == 5) || ((t / 128) % 3 == 1 && (m / 32) % 2 == 0) || (t > m + r * c.M);
+            mask[r][((size_t)i1 * c.M + m) * T + t] = v;
+          }
+    }
+  }
+  // ---- reference
+  std::vector<std::vector<double>> rA(W), rB(W), rV(W), gA(W), gB(W), gV(W);  // values and magnitudes
+  std::vector<std::vector<float>> neg_lse(W), nds(W);
+  for (int r = 0; r < W; ++r) {
+    rA[r].assign((size_t)Bt * c.M * c.d, 0); gA[r] = rA[r];
+    rB[r].assign((size_t)Bt * c.Tn * c.d, 0); gB[r] = rB[r];
+    rV[r].assign((size_t)Bt * c.Tn * c.dv, 0); gV[r] = rV[r];
+    neg_lse[r].assign((size_t)Bt * stat_ld, 0.f);
+    nds[r].assign((size_t)Bt * stat_ld, 0.f);
+  }
+  std::vector<double> s(T), pj(T), dsv(T), orow(c.dv);
+  for (int r = 0; r < W; ++r)
+    for (int i1 = 0; i1 < c.b1; ++i1)
+      for (int i0 = 0; i0 < c.b0; ++i0) {
+        const int b = i1 * c.b0 + i0;
+        for (int m = 0; m < c.M; ++m) {
+          double mx = -INFINITY;
+          for (int t = 0; t < T; ++t) {
+            const int src = t / c.Tn, j = t % c.Tn;
+            double acc = 0;
+            for (int k = 0; k < c.d; ++k) acc += (double)A[r].at(i1, i0, m, k) * B[src].at(i1, i0, j, k);
+            const bool dead = c.maskmode && mask[r][((size_t)i1 * c.M + m) * T + t];
+            s[t] = dead ? -INFINITY : acc * sl2;
+            if (s[t] > mx) mx = s[t];
+          }
+          if (mx == -INFINITY) continue;  // fully masked row: contributes nothing (statistics stay 0)
+          double l = 0;
+          for (int t = 0; t < T; ++t) {
+            pj[t] = exp2(s[t] - mx);
+            l += pj[t];
+          }
+          for (int n = 0; n < c.dv; ++n) orow[n] = 0;
+          for (int t = 0; t < T; ++t) {
+            pj[t] /= l;
+            for (int n = 0; n < c.dv; ++n) orow[n] += pj[t] * V[t / c.Tn].at(i1, i0, t % c.Tn, n);
+          }
+          double delta = 0;
+          for (int n = 0; n < c.dv; ++n) delta += (double)G[r].at(i1, i0, m, n) * orow[n];
+          neg_lse[r][(size_t)b * stat_ld + m] = (float)-(mx + log2(l));
+          nds[r][(size_t)b * stat_ld + m] = (float)(-(double)scale * delta);
+          for (int t = 0; t < T; ++t) {
+            const int src = t / c.Tn, j = t % c.Tn;
+            double dp = 0;
+            for (int n = 0; n < c.dv; ++n) dp += (double)G[r].at(i1, i0, m, n) * V[src].at(i1, i0, j, n);
+            const double ds = scale * pj[t] * (dp - delta);
+            dsv[t] = ds;
+            for (int k = 0; k < c.d; ++k) {
+              const double ta = ds * B[src].at(i1, i0, j, k), tb = ds * A[r].at(i1, i0, m, k);
+              rA[r][((size_t)b * c.M + m) * c.d + k] += ta;
+              gA[r][((size_t)b * c.M + m) * c.d + k] += fabs(ta);
+              rB[src][((size_t)b * c.Tn + j) * c.d + k] += tb;
+              gB[src][((size_t)b * c.Tn + j) * c.d + k] += fabs(tb);
+            }
+            for (int n = 0; n < c.dv; ++n) {
+              const double tv = pj[t] * G[r].at(i1, i0, m, n);
+              rV[src][((size_t)b * c.Tn + j) * c.dv + n] += tv;
+              gV[src][((size_t)b * c.Tn + j) * c.dv + n] += fabs(tv);
+            }
+          }
+        }
+      }
+  // ---- device
+  std::vector<void*> dAp(W), dBp(W), dVp(W), dGp(W), ddA(W), ddB(W), ddV(W), dMask(W, nullptr), dBits(W, nullptr),
+      dBitsT(W, nullptr), dNl(W), dNd(W);
+  const long long ldw = (T + 31) / 32, ldwt = (c.M + 31) / 32;
+  for (int r = 0; r < W; ++r) {
+    CK(cudaMalloc(&dAp[r], A[r].size() * 2)); to_dev(A[r].v, c.dt, dAp[r]);
+    CK(cudaMalloc(&dBp[r], B[r].size() * 2)); to_dev(B[r].v, c.dt, dBp[r]);
+    CK(cudaMalloc(&dVp[r], V[r].size() * 2)); to_dev(V[r].v, c.dt, dVp[r]);
+    CK(cudaMalloc(&dGp[r], G[r].size() * 2)); to_dev(G[r].v, c.dt, dGp[r]);
+    CK(cudaMalloc(&ddA[r], dA[r].size() * 2)); CK(cudaMemset(ddA[r], 0xFF, dA[r].size() * 2));
+    CK(cudaMalloc(&ddB[r], dB[r].size() * 2)); CK(cudaMemset(ddB[r], 0xFF, dB[r].size() * 2));
+    CK(cudaMalloc(&ddV[r], dV[r].size() * 2)); CK(cudaMemset(ddV[r], 0xFF, dV[r].size() * 2));
+    CK(cudaMalloc(&dNl[r], neg_lse[r].size() * 4 + 256));
+    CK(cudaMemcpy(dNl[r], neg_lse[r].data(), neg_lse[r].size() * 4, cudaMemcpyHostToDevice));
+    CK(cudaMalloc(&dNd[r], nds[r].size() * 4 + 256));
+    CK(cudaMemcpy(dNd[r], nds[r].data(), nds[r].size() * 4, cudaMemcpyHostToDevice));
+    if (c.maskmode) {
+      CK(cudaMalloc(&dMask[r], mask[r].size()));
+      CK(cudaMemcpy(dMask[r], mask[r].data(), mask[r].size(), cudaMemcpyHostToDevice));
+      CK(cudaMalloc(&dBits[r], (size_t)c.b1 * c.M * ldw * 4));
+      CK(cudaMalloc(&dBitsT[r], (size_t)c.b1 * T * ldwt * 4));
+      if (ddp_pack_mask((const uint8_t*)dMask[r], c.b1, c.M, T, T, (long long)c.M * T, (uint32_t*)dBits[r], ldw, 0) ||
+          ddp_pack_mask_t((const uint8_t*)dMask[r], c.b1, c.M, T, T, (long long)c.M * T, (uint32_t*)dBitsT[r], ldwt, 0)) {
+        printf("pack_mask failed: %s\n", ddp_last_error());
+        return false;
+      }
+    }
+  }
+  std::vector<void*> ws(W, nullptr);
+  std::vector<uint32_t*> flags(W, nullptr), done(W, nullptr), exitc(W, nullptr);
+  if (W > 1) {
+    size_t wsb = 0, nf = 0, wsb2 = 0, nf2 = 0;
+    ddp_tensor b0 = dview(B[0], dBp[0], c.dt), v0 = dview(V[0], dVp[0], c.dt);
+    ddp_attn_fwd_workspace(&b0, &v0, W, c.chunk, &wsb, &nf);
+    ddp_attn_bwd_cols_workspace(&b0, &v0, W, c.chunk, &wsb2, &nf2);
+    if (wsb2 > wsb) wsb = wsb2;
+    if (nf2 > nf) nf = nf2;
+    for (int r = 0; r < W; ++r) {
+      CK(cudaMalloc(&ws[r], wsb + 256)); CK(cudaMemset(ws[r], 0xFF, wsb + 256));
+      CK(cudaMalloc((void**)&flags[r], nf * 4 + 256)); CK(cudaMemset(flags[r], 0, nf * 4 + 256));
+      CK(cudaMalloc((void**)&done[r], 256)); CK(cudaMemset(done[r], 0, 256));
+      CK(cudaMalloc((void**)&exitc[r], 256)); CK(cudaMemset(exitc[r], 0, 256));
+    }
+  }
+  bool ok = true;
+  uint32_t seq = 0;
+  for (int kernel = 0; kernel < 2 && ok; ++kernel) {
+    ++seq;
+    const int phases_rows[2] = {1, 2}, phases_cols[3] = {1, 2, 4};
+    const int nph = (W > 1) ? (kernel ? 3 : 2) : 1;
+    for (int pi = 0; pi < nph && ok; ++pi) {
+      const int phase = (W > 1) ? (kernel ? phases_cols[pi] : phases_rows[pi]) : 3;
+      for (int r = 0; r < W; ++r) {
+        ddp_comm cm;
+        memset(&cm, 0, sizeof cm);
+        cm.world = W; cm.rank = r; cm.seq = seq; cm.phase_mask = phase; cm.chunk_rows = c.chunk;
+        for (int q = 0; q < W; ++q) {
+          cm.ws[q] = ws[q]; cm.flags[q] = flags[q]; cm.done[q] = done[q];
+        }
+        cm.exit_counter = exitc[r];
+        ddp_tensor a = dview(A[r], dAp[r], c.dt), b = dview(B[r], dBp[r], c.dt), v = dview(V[r], dVp[r], c.dt),
+                   g = dview(G[r], dGp[r], c.dt), oa = dview(dA[r], ddA[r], c.dt), ob = dview(dB[r], ddB[r], c.dt),
+                   ov = dview(dV[r], ddV[r], c.dt);
+        int e;
+        if (kernel == 0)
+          e = ddp_attn_bwd_rows(&a, &g, &b, &v, &oa, (const float*)dNl[r], (const float*)dNd[r], stat_ld,
+                                (const uint32_t*)dBits[r], ldw, (long long)c.M * ldw, scale, W > 1 ? &cm : nullptr, 0, 0);
+        else
+          e = ddp_attn_bwd_cols(&a, &g, &b, &v, &ov, &ob, (const float*)dNl[r], (const float*)dNd[r], stat_ld,
+                                (const uint32_t*)dBitsT[r], ldwt, (long long)T * ldwt, scale, W > 1 ? &cm : nullptr, 0, 0);
+        if (e) {
+          printf("  backward kernel %d error %d: %s\n", kernel, e, ddp_last_error());
+          ok = false;
+          break;
+        }
+      }
+      cudaError_t e = cudaDeviceSynchronize();
+      if (e != cudaSuccess) {
+        printf("  kernel fault (kernel %d phase %d): %s\n", kernel, phase, cudaGetErrorString(e));
+        exit(3);
+      }
+    }
+    const int site = ddp_debug_timeout_site_attn();
+    if (site) {
+      printf("  pipeline watchdog fired at site %d (kernel %d)\n", site, kernel);
+      ok = false;
+    }
+  }
+  // ---- compare
+  double maxerr[3] = {0, 0, 0};
+  long long nbad[3] = {0, 0, 0};
+  if (ok) {
+    for (int r = 0; r < W; ++r) {
+      for (int which = 0; which < 3; ++which) {
+        const HT& t = which == 0 ? dA[r] : which == 1 ? dB[r] : dV[r];
+        const void* dp = which == 0 ? ddA[r] : which == 1 ? ddB[r] : ddV[r];
+        const std::vector<double>& ref = which == 0 ? rA[r] : which == 1 ? rB[r] : rV[r];
+        const std::vector<double>& mag = which == 0 ? gA[r] : which == 1 ? gB[r] : gV[r];
+        std::vector<float> got = from_dev(dp, t.size(), c.dt);
+        int shown = 0;
+        for (int i1 = 0; i1 < c.b1; ++i1)
+          for (int i0 = 0; i0 < c.b0; ++i0)
+            for (int m = 0; m < t.rows; ++m)
+              for (int n = 0; n < t.cols; ++n) {
+                const size_t ri = ((size_t)(i1 * c.b0 + i0) * t.rows + m) * t.cols + n;
+                const float g = got[i1 * t.sb1 + i0 * t.sb0 + (long long)m * t.ld + n];
+                const double err = fabs((double)g - ref[ri]);
+                const bool bad = !(err <= 0.01 * mag[ri] + 0.01 * fabs(ref[ri]) + 2e-3);
+                if (err == err && err > maxerr[which]) maxerr[which] = err;
+                if (bad) {
+                  ++nbad[which];
+                  if (verbose && shown < 5) {
+                    printf("    bad %s rank %d b(%d,%d) row %d col %d: got %g want %g\n",
+                           which == 0 ? "dA" : which == 1 ? "dB" : "dV", r, i1, i0, m, n, g, ref[ri]);
+                    ++shown;
+                  }
+                }
+              }
+      }
+    }
+    if (nbad[0] || nbad[1] || nbad[2]) ok = false;
+  }
+  printf("%s ATTN-BWD %s W=%d b=(%d,%d) M=%d Tn=%d d=%d dv=%d il=%d mask=%d chunk=%d  dA err=%.3g bad=%lld  dB err=%.3g "
+         "bad=%lld  dV err=%.3g bad=%lld\n",
+         ok ? "PASS" : "FAIL", c.dt == DDP_BF16 ? "bf16" : "fp16", W, c.b1, c.b0, c.M, c.Tn, c.d, c.dv, (int)c.interleave,
+         c.maskmode, c.chunk, maxerr[0], nbad[0], maxerr[1], nbad[1], maxerr[2], nbad[2]);
+  fflush(stdout);
+  for (int r = 0; r < W; ++r) {
+    cudaFree(dAp[r]); cudaFree(dBp[r]); cudaFree(dVp[r]); cudaFree(dGp[r]); cudaFree(ddA[r]); cudaFree(ddB[r]);
+    cudaFree(ddV[r]); cudaFree(dNl[r]); cudaFree(dNd[r]);
+    if (dMask[r]) cudaFree(dMask[r]);
+    if (dBits[r]) cudaFree(dBits[r]);
+    if (dBitsT[r]) cudaFree(dBitsT[r]);
+    if (W > 1) { cudaFree(ws[r]); cudaFree(flags[r]); cudaFree(done[r]); cudaFree(exitc[r]); }
+  }
+  if (ok) ++g_pass; else ++g_fail;
+  return ok;
+}
+
+static void perf_bwd(int dt, int H, int M, int Tn, int d, int iters) {
+  HT A = make_ht(1, H, M, d, true, false), B = make_ht(1, H, Tn, d, true, false);
+  void *dA_, *dB_, *dV_, *dG_, *oA, *oB, *oV;
+  float *nl, *nd;
+  CK(cudaMalloc(&dA_, A.size() * 2)); CK(cudaMalloc(&dG_, A.size() * 2)); CK(cudaMalloc(&oA, A.size() * 2));
+  CK(cudaMalloc(&dB_, B.size() * 2)); CK(cudaMalloc(&dV_, B.size() * 2)); CK(cudaMalloc(&oB, B.size() * 2));
+  CK(cudaMalloc(&oV, B.size() * 2));
+  CK(cudaMemset(dA_, 0x3c, A.size() * 2)); CK(cudaMemset(dG_, 0x3c, A.size() * 2));
+  CK(cudaMemset(dB_, 0x3c, B.size() * 2)); CK(cudaMemset(dV_, 0x3c, B.size() * 2));
+  CK(cudaMalloc((void**)&nl, (size_t)H * M * 4)); CK(cudaMemset(nl, 0, (size_t)H * M * 4));
+  CK(cudaMalloc((void**)&nd, (size_t)H * M * 4)); CK(cudaMemset(nd, 0, (size_t)H * M * 4));
+  ddp_tensor a = dview(A, dA_, dt), g = dview(A, dG_, dt), b = dview(B, dB_, dt), v = dview(B, dV_, dt),
+             oa = dview(A, oA, dt), ob = dview(B, oB, dt), ov = dview(B, oV, dt);
+  const float scale = 1.0f / sqrtf((float)d);
+  cudaEvent_t e0, e1, e2;
+  CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1)); CK(cudaEventCreate(&e2));
+  for (int i = 0; i < 2; ++i) {
+    if (ddp_attn_bwd_rows(&a, &g, &b, &v, &oa, nl, nd, M, nullptr, 0, 0, scale, nullptr, 0, 0) ||
+        ddp_attn_bwd_cols(&a, &g, &b, &v, &ov, &ob, nl, nd, M, nullptr, 0, 0, scale, nullptr, 0, 0)) {
+      printf("perf launch failed: %s\n", ddp_last_error());
+      return;
+    }
+  }
+  CK(cudaDeviceSynchronize());
+  CK(cudaEventRecord(e0));
+  for (int i = 0; i < iters; ++i) ddp_attn_bwd_rows(&a, &g, &b, &v, &oa, nl, nd, M, nullptr, 0, 0, scale, nullptr, 0, 0);
+  CK(cudaEventRecord(e1));
+  for (int i = 0; i < iters; ++i) ddp_attn_bwd_cols(&a, &g, &b, &v, &ov, &ob, nl, nd, M, nullptr, 0, 0, scale, nullptr, 0, 0);
+  CK(cudaEventRecord(e2));
+  CK(cudaEventSynchronize(e2));
+  float ms_r, ms_c;
+  CK(cudaEventElapsedTime(&ms_r, e0, e1));
+  CK(cudaEventElapsedTime(&ms_c, e1, e2));
+  ms_r /= iters; ms_c /= iters;
+  const double tile = 2.0 * H * (double)M * Tn * d;
+  const int site = ddp_debug_timeout_site_attn();
+  printf("PERF ATTN-BWD %s H=%d M=%d T=%d d=%d: rows (dA) %.3f ms %.1f TFLOP/s   cols (dB, dV) %.3f ms %.1f TFLOP/s%s\n",
+         dt == DDP_BF16 ? "bf16" : "fp16", H, M, Tn, d, ms_r, 3 * tile / ms_r * 1e-9, ms_c, 4 * tile / ms_c * 1e-9,
+         site ? "  WATCHDOG FIRED" : "");
+  fflush(stdout);
+}
+
 static void perf_case(int dt, int H, int M, int Tn, int d, bool with_mask, int iters, int dbg = 0) {
   HT A = make_ht(1, H, M, d, true, false), B = make_ht(1, H, Tn, d, true, false), V = make_ht(1, H, Tn, d, true, false),
      O = make_ht(1, H, M, d, true, false);
@@ -353,7 +627,7 @@ int main(int argc, char** argv) {
     run_case(c, argc > 14 ? atoi(argv[14]) : 0, true);
     return g_fail ? 1 : 0;
   }
-  if (mode != "perf") {
+  if (mode != "perf" && mode != "bwd" && mode != "bwdfull") {
     const int bf = DDP_BF16;
     //        dt  W b1 b0 M    Tn   d   dv  il     mask chunk ramp
     // stage 1: linear mode (no max / exp): isolates S MMA -> P staging -> PV MMA -> O store
@@ -384,6 +658,23 @@ int main(int argc, char** argv) {
       run_case({bf, 4, 1, 3, 100, 96, 64, 64, false, 1, 32, 0}, 0, true);
     }
     printf("SUMMARY pass=%d fail=%d\n", g_pass, g_fail);
+  }
+  if (mode == "bwd" || mode == "bwdfull") {
+    const int bf = DDP_BF16;
+    //            dt  W b1 b0 M    Tn   d   dv  il     mask chunk ramp
+    run_bwd_case({bf, 1, 1, 1, 256, 128, 64, 64, false, 0, 64, 0}, true);
+    run_bwd_case({bf, 1, 1, 2, 256, 512, 64, 64, true, 1, 64, 0}, true);
+    run_bwd_case({bf, 1, 2, 3, 200, 300, 32, 32, true, 2, 64, 0}, true);
+    run_bwd_case({bf, 1, 1, 2, 100, 72, 40, 24, false, 1, 64, 0}, true);
+    run_bwd_case({DDP_F16, 1, 1, 2, 384, 256, 64, 64, true, 1, 64, 0}, true);
+    run_bwd_case({bf, 1, 1, 4, 1024, 1024, 64, 64, true, 0, 64, 0}, true);
+    run_bwd_case({bf, 2, 1, 2, 256, 256, 64, 64, true, 0, 64, 0}, true);
+    run_bwd_case({bf, 2, 1, 2, 256, 256, 64, 64, true, 1, 128, 0}, true);
+    run_bwd_case({bf, 4, 2, 2, 160, 160, 32, 32, true, 2, 64, 0}, true);
+    run_bwd_case({bf, 4, 1, 3, 100, 96, 64, 64, false, 1, 32, 0}, true);
+    printf("SUMMARY-BWD pass=%d fail=%d\n", g_pass, g_fail);
+    if (mode == "bwdfull") perf_bwd(DDP_BF16, 16, 8192, 8192, 64, 5);
+    return g_fail ? 1 : 0;
   }
   if (mode == "perf" || mode == "full") {
     perf_case(DDP_BF16, 16, 8192, 8192, 64, false, 5);

@@ -122,7 +122,31 @@ int ddp_attn_fwd_workspace(const ddp_tensor* B, const ddp_tensor* V, int world, 
 int ddp_attn_fwd(const ddp_tensor* A, const ddp_tensor* B, const ddp_tensor* V, const ddp_tensor* O, float* lse,
                  const uint32_t* mask_bits, int64_t mask_ld_words, int64_t mask_sb1_words, float scale,
                  const ddp_comm* comm, int dbg, void* stream);
-int ddp_debug_timeout_site_attn(void); /* pipeline watchdog of the attention kernel (sites 11-19) */
+/* Slab-free attention backward (autograd of module.py:61-69), two deterministic kernels that recompute the
+ * probabilities from the forward's log-sum-exp instead of reading a saved slab:
+ *   rows:  dA[b1][b0][M][d]  = sum_j dS_ij gather(B)_j                  (all-gather of B, V fused in)
+ *   cols:  dV[b1][b0][Tn][dv] = sum_ranks sum_i P_ij dO_i,  dB likewise with dS and A
+ *          (all-gather of B, V AND the reduce-scatter of the per-rank partial sums fused in)
+ * with P_ij = exp2(scale*log2e*A_i.B_j + neg_lse_i), dS_ij = P_ij*(scale*dO_i.V_j + nds_i); G = dO.
+ * neg_lse = -L and nds = -scale*rowsum(dO*O) are fp32 [b1][b0][stat_ld] arrays, stat_ld a multiple of 64 >= M
+ * (rows past M are read but ignored).  mask_bits: as for ddp_attn_fwd; mask_bits_t: the TRANSPOSED packing of
+ * ddp_pack_mask_t ([b1][T][ld_words], bits along the rows).  Same shape limits as ddp_attn_fwd (error -6).
+ * ddp_attn_bwd_rows uses the workspace of ddp_attn_fwd_workspace; ddp_attn_bwd_cols its own. */
+int ddp_attn_bwd_rows(const ddp_tensor* A, const ddp_tensor* G, const ddp_tensor* B, const ddp_tensor* V,
+                      const ddp_tensor* dA, const float* neg_lse, const float* nds, int64_t stat_ld,
+                      const uint32_t* mask_bits, int64_t mask_ld_words, int64_t mask_sb1_words, float scale,
+                      const ddp_comm* comm, int dbg, void* stream);
+int ddp_attn_bwd_cols_workspace(const ddp_tensor* B, const ddp_tensor* V, int world, int chunk_rows, size_t* ws_bytes,
+                                size_t* n_flags);
+int ddp_attn_bwd_cols(const ddp_tensor* A, const ddp_tensor* G, const ddp_tensor* B, const ddp_tensor* V,
+                      const ddp_tensor* dV, const ddp_tensor* dB, const float* neg_lse, const float* nds,
+                      int64_t stat_ld, const uint32_t* mask_bits_t, int64_t mask_ld_words, int64_t mask_sb1_words,
+                      float scale, const ddp_comm* comm, int dbg, void* stream);
+/* bits_t[b1][cols][ld_words] <- mask u8 [b1][rows][cols]: bit (r & 31) of word r >> 5 = mask[r][col] != 0;
+ * bits past `rows` are set. */
+int ddp_pack_mask_t(const uint8_t* mask, int64_t b1, int64_t rows, int64_t cols, int64_t mask_ld, int64_t mask_sb1,
+                    uint32_t* bits_t, int64_t ld_words, void* stream);
+int ddp_debug_timeout_site_attn(void); /* pipeline watchdog of the attention kernels (sites 11-40) */
 
 /* Row softmax over the last dim of x[b1][b0][rows][cols] with fused scale and boolean mask:
  *   y = softmax(scale * x  masked_fill(mask, -inf))     (reference: module.py:65-67)
