@@ -96,6 +96,14 @@ def load():
         lib.ddp_attn_fwd.argtypes = [tp, tp, tp, tp, c.c_void_p, c.c_void_p, c.c_int64, c.c_int64, c.c_float,
                                      c.POINTER(Comm), c.c_int, c.c_void_p]
         lib.ddp_debug_timeout_site_attn.restype = c.c_int
+        lib.ddp_attn_bwd_rows.argtypes = [tp, tp, tp, tp, tp, c.c_void_p, c.c_void_p, c.c_int64, c.c_void_p, c.c_int64,
+                                          c.c_int64, c.c_float, c.POINTER(Comm), c.c_int, c.c_void_p]
+        lib.ddp_attn_bwd_cols_workspace.argtypes = [tp, tp, c.c_int, c.c_int, c.POINTER(c.c_size_t),
+                                                    c.POINTER(c.c_size_t)]
+        lib.ddp_attn_bwd_cols.argtypes = [tp, tp, tp, tp, tp, tp, c.c_void_p, c.c_void_p, c.c_int64, c.c_void_p,
+                                          c.c_int64, c.c_int64, c.c_float, c.POINTER(Comm), c.c_int, c.c_void_p]
+        lib.ddp_pack_mask_t.argtypes = [c.c_void_p, c.c_int64, c.c_int64, c.c_int64, c.c_int64, c.c_int64, c.c_void_p,
+                                        c.c_int64, c.c_void_p]
         lib.ddp_debug_timeout_site.restype = c.c_int
         lib.ddp_debug_timeout_site_rowops.restype = c.c_int
         lib.ddp_read_u32.argtypes = [c.c_void_p, c.POINTER(c.c_uint32)]

@@ -107,27 +107,23 @@ def flash_eligible(k4, q4, v4, mask, world):
     return all(_g._aligned(t) for t in (k4, q4, v4))
 
 
-def flash_attention_forward(k4, q4, v4, mask, scale, offset, out4, want_lse=False):
+def flash_attention_forward(k4, q4, v4, mask, scale, offset, out4, want_lse=False, bits=None):
     """``out4 = softmax(scale * k4 @ gather(q4)^T masked) @ gather(v4)`` in ONE kernel (reference:
     module.py:61-69): scores stay in TMEM, probabilities go through shared memory back into the tensor
     core, the ``[T/N, T]`` slab is never written; the all-gather of ``q4`` / ``v4`` is fused in.
     Returns the fp32 row log-sum-exp (log2 domain) if ``want_lse``."""
     import ctypes
-    from distributed_dot_product.ops.softmax import _prep_mask
     from distributed_dot_product.parallel import runtime
     lib = _native.load()
     world = runtime.get_world_size()
     b, h, tn, _ = k4.shape
     total = world * q4.size(-2)
-    bits, ldw, sb1w = None, 0, 0
+    ldw = sb1w = 0
     if mask is not None:
-        mu8, m_ld, m_sb1 = _prep_mask(mask, torch.empty((b, h, tn, total), device='meta'))
-        ldw = (total + 31) // 32
-        bits = torch.empty(b, tn, ldw, dtype=torch.int32, device=k4.device)
-        _native.check(lib.ddp_pack_mask(ctypes.c_void_p(mu8.data_ptr()), b, tn, total, m_ld, m_sb1,
-                                        ctypes.c_void_p(bits.data_ptr()), ldw, _g._stream()))
-        _native.count_launch()
-        sb1w = tn * ldw
+        if bits is None:
+            bits, ldw, sb1w = _pack_mask(mask, b, h, tn, total, k4.device)
+        else:
+            ldw, sb1w = bits.size(-1), tn * bits.size(-1)
     lse = torch.empty(b, h, tn, dtype=torch.float32, device=k4.device) if want_lse else None
     va, vb, vv, vo = _g.as_view(k4), _g.as_view(q4), _g.as_view(v4), _g.as_view(out4)
     comm_ptr = None
@@ -145,6 +141,76 @@ def flash_attention_forward(k4, q4, v4, mask, scale, offset, out4, want_lse=Fals
                                    float(scale), comm_ptr, 0, _g._stream()))
     _native.count_launch()
     return lse
+
+
+def _pack_mask(mask, b, h, tn, total, device, transposed=False):
+    """Bit-packs a bool ``[B, T/N, T]`` mask (True = masked out): along the columns (``[B, T/N, T/32]``) for the
+    row-side kernels, or transposed (``[B, T, ceil(T/N / 32)]``, bits along the rows) for the column-side one."""
+    import ctypes
+    from distributed_dot_product.ops.softmax import _prep_mask
+    lib = _native.load()
+    mu8, m_ld, m_sb1 = _prep_mask(mask, torch.empty((b, h, tn, total), device='meta'))
+    if transposed:
+        ldw = (tn + 31) // 32
+        bits = torch.empty(b, total, ldw, dtype=torch.int32, device=device)
+        _native.check(lib.ddp_pack_mask_t(ctypes.c_void_p(mu8.data_ptr()), b, tn, total, m_ld, m_sb1,
+                                          ctypes.c_void_p(bits.data_ptr()), ldw, _g._stream()))
+        sb1w = total * ldw
+    else:
+        ldw = (total + 31) // 32
+        bits = torch.empty(b, tn, ldw, dtype=torch.int32, device=device)
+        _native.check(lib.ddp_pack_mask(ctypes.c_void_p(mu8.data_ptr()), b, tn, total, m_ld, m_sb1,
+                                        ctypes.c_void_p(bits.data_ptr()), ldw, _g._stream()))
+        sb1w = tn * ldw
+    _native.count_launch()
+    return bits, ldw, sb1w
+
+
+def flash_attention_backward(k4, q4, v4, g4, neg_lse, nds, mask, scale, offset, dk4, dq4, dv4, bits=None):
+    """Backward of ``flash_attention_forward`` without any ``[T/N, T]`` slab: two deterministic kernels recompute
+    the probability tiles from the forward's log-sum-exp (``neg_lse = -L``, ``nds = -scale * rowsum(dO * O)``,
+    both fp32 ``[B, H, stat_ld]`` with ``stat_ld`` a multiple of 64).  ``dk4`` gets the row-side gradient
+    (all-gather of q / v fused in), ``dq4`` / ``dv4`` the column-side ones (all-gather AND the reduce-scatter of
+    the ranks' partial sums fused in)."""
+    import ctypes
+    from distributed_dot_product.parallel import runtime
+    lib = _native.load()
+    world = runtime.get_world_size()
+    b, h, tn, _ = k4.shape
+    total = world * q4.size(-2)
+    stat_ld = neg_lse.size(-1)
+    ldw = sb1w = ldwt = sb1wt = 0
+    bits_t = None
+    if mask is not None:
+        if bits is None:
+            bits, ldw, sb1w = _pack_mask(mask, b, h, tn, total, k4.device)
+        else:
+            ldw, sb1w = bits.size(-1), tn * bits.size(-1)
+        bits_t, ldwt, sb1wt = _pack_mask(mask, b, h, tn, total, k4.device, transposed=True)
+    va, vb, vv, vg = _g.as_view(k4), _g.as_view(q4), _g.as_view(v4), _g.as_view(g4)
+    vda, vdb, vdv = _g.as_view(dk4), _g.as_view(dq4), _g.as_view(dv4)
+    nl, nd = ctypes.c_void_p(neg_lse.data_ptr()), ctypes.c_void_p(nds.data_ptr())
+    chunk = _g.chunk_rows_from_offset(offset, q4.size(-2), 2 * b * h)
+
+    def comm_for(ws_fn):
+        if world == 1:
+            return None
+        ws, nf = ctypes.c_size_t(), ctypes.c_size_t()
+        _native.check(ws_fn(ctypes.byref(vb), ctypes.byref(vv), world, chunk, ctypes.byref(ws), ctypes.byref(nf)))
+        hp = runtime.heap()
+        hp.ensure(ws.value, nf.value)
+        return ctypes.byref(hp.next_comm(chunk))
+
+    _native.check(lib.ddp_attn_bwd_rows(
+        ctypes.byref(va), ctypes.byref(vg), ctypes.byref(vb), ctypes.byref(vv), ctypes.byref(vda), nl, nd, stat_ld,
+        ctypes.c_void_p(bits.data_ptr()) if bits is not None else None, ldw, sb1w, float(scale),
+        comm_for(lib.ddp_attn_fwd_workspace), 0, _g._stream()))
+    _native.count_launch()
+    _native.check(lib.ddp_attn_bwd_cols(
+        ctypes.byref(va), ctypes.byref(vg), ctypes.byref(vb), ctypes.byref(vv), ctypes.byref(vdv), ctypes.byref(vdb),
+        nl, nd, stat_ld, ctypes.c_void_p(bits_t.data_ptr()) if bits_t is not None else None, ldwt, sb1wt,
+        float(scale), comm_for(lib.ddp_attn_bwd_cols_workspace), 0, _g._stream()))
+    _native.count_launch()
 
 
 def _rowdot(a, b):
@@ -213,6 +279,53 @@ class _AttentionCore(torch.autograd.Function):
         return d_keys, d_queries, d_values, None, None, None, None
 
 
+class _FlashAttentionCore(torch.autograd.Function):
+    """Training path without the probability slab: the forward keeps only O and the row log-sum-exp, the
+    backward recomputes the tiles (``flash_attention_backward``).  Memory per rank is O(T/N * H * d) instead of
+    O(T/N * T * H); a fully masked row yields NaN in the forward (as the reference) and zero gradients."""
+
+    @staticmethod
+    def forward(ctx, keys, queries, values, mask, num_heads, scale, offset):
+        k4, q4, v4 = _heads(keys, num_heads), _heads(queries, num_heads), _heads(values, num_heads)
+        b, h, tn, _ = k4.shape
+        from distributed_dot_product.parallel import runtime
+        total = runtime.get_world_size() * q4.size(-2)
+        bits = None
+        if mask is not None:
+            bits, _, _ = _pack_mask(mask, b, h, tn, total, keys.device)
+        out = torch.empty(keys.shape[:-1] + (values.size(-1),), dtype=values.dtype, device=values.device)
+        lse = flash_attention_forward(k4, q4, v4, mask, scale, offset, _heads(out, num_heads), want_lse=True,
+                                      bits=bits)
+        ctx.save_for_backward(keys, queries, values, out, lse, mask, bits)
+        ctx.num_heads, ctx.scale, ctx.offset = num_heads, scale, offset
+        return out
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        keys, queries, values, out, lse, mask, bits = ctx.saved_tensors
+        h, scale, offset = ctx.num_heads, ctx.scale, ctx.offset
+        if not grad_out.is_contiguous():
+            grad_out = grad_out.contiguous()
+        b, tn, hd = grad_out.shape
+        dv = hd // h
+        # delta_i = rowsum(dO_i * O_i) per (row, head); the kernels want -L and -scale*delta as [B, H, stat_ld]
+        delta = _rowdot(grad_out.view(b * tn * h, dv), out.view(b * tn * h, dv)).view(b, tn, h)
+        stat_ld = (tn + 63) // 64 * 64
+        neg_lse = torch.zeros(b, h, stat_ld, dtype=torch.float32, device=keys.device)
+        nds = torch.zeros(b, h, stat_ld, dtype=torch.float32, device=keys.device)
+        neg_lse[..., :tn] = torch.nan_to_num(-lse, nan=0.0, posinf=0.0, neginf=0.0)
+        nds[..., :tn] = torch.nan_to_num(delta.transpose(1, 2) * (-scale), nan=0.0, posinf=0.0, neginf=0.0)
+        d_keys, d_queries, d_values = torch.empty_like(keys), torch.empty_like(queries), torch.empty_like(values)
+        flash_attention_backward(_heads(keys, h), _heads(queries, h), _heads(values, h), _heads(grad_out, h),
+                                 neg_lse, nds, mask, scale, offset, _heads(d_keys, h), _heads(d_queries, h),
+                                 _heads(d_values, h), bits=bits)
+        return d_keys, d_queries, d_values, None, None, None, None
+
+
+#: train through the slab-free kernels too (forward keeps O + log-sum-exp, backward recomputes the tiles)
+FLASH_TRAIN = bool(int(__import__('os').environ.get('DDP_FLASH_TRAIN', '1')))
+
+
 def attention_core(keys, queries, values, mask, num_heads, scale, offset=32):
     """``softmax(scale * K Q^T masked) V`` with K/Q/V given as ``[B, T/N, H*d]`` projections.
 
@@ -226,4 +339,9 @@ def attention_core(keys, queries, values, mask, num_heads, scale, offset=32):
             out = torch.empty(keys.shape[:-1] + (values.size(-1),), dtype=values.dtype, device=values.device)
             flash_attention_forward(k4, q4, v4, mask, scale, offset, _heads(out, num_heads))
             return out
+    if FLASH_TRAIN and needs_grad and scale > 0:
+        from distributed_dot_product.parallel import runtime
+        k4, q4, v4 = _heads(keys, num_heads), _heads(queries, num_heads), _heads(values, num_heads)
+        if flash_eligible(k4, q4, v4, mask, runtime.get_world_size()) and k4.size(-2) == q4.size(-2):
+            return _FlashAttentionCore.apply(keys, queries, values, mask, num_heads, scale, offset)
     return _AttentionCore.apply(keys, queries, values, mask, num_heads, scale, offset)

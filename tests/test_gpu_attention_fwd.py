@@ -101,3 +101,50 @@ def test_attention_harness_emulated_ranks(cuda_device):
     tail = '\n'.join(r.stdout.splitlines()[-20:])
     assert r.returncode == 0, tail
     assert 'fail=0' in r.stdout, tail
+
+
+@pytest.mark.parametrize('heads,tn,d,masked', [(4, 384, 64, True), (2, 200, 32, True), (16, 256, 64, False)])
+def test_flash_training_matches_slab_path(cuda_device, heads, tn, d, masked):
+    """Gradients of the slab-free training path (forward keeps O + log-sum-exp, two backward kernels recompute
+    the tiles) against the slab path of the same layer and against an fp32 autograd reference."""
+    import distributed_dot_product.ops.attention as att
+    torch.manual_seed(3)
+    b = 2
+    k = torch.randn(b, tn, heads * d, device=cuda_device).to(torch.bfloat16)
+    q = torch.randn(b, tn, heads * d, device=cuda_device).to(torch.bfloat16)
+    v = torch.randn(b, tn, heads * d, device=cuda_device).to(torch.bfloat16)
+    g = torch.randn(b, tn, heads * d, device=cuda_device).to(torch.bfloat16)
+    mask = (torch.rand(b, tn, tn, device=cuda_device) < 0.3) if masked else None
+    scale = 1.0 / math.sqrt(d)
+
+    def run(flash):
+        old = att.FLASH_TRAIN
+        att.FLASH_TRAIN = flash
+        try:
+            kk, qq, vv = (t.clone().requires_grad_(True) for t in (k, q, v))
+            out = att.attention_core(kk, qq, vv, mask, heads, scale, 64)
+            out.backward(g)
+            return out.detach().float(), kk.grad.float(), qq.grad.float(), vv.grad.float()
+        finally:
+            att.FLASH_TRAIN = old
+
+    kf, qf, vf = (t.float().requires_grad_(True) for t in (k, q, v))
+    ref_out = _reference(kf, qf, vf, mask, heads, scale)
+    ref_out.backward(g.float())
+    ref = (ref_out.detach(), kf.grad, qf.grad, vf.grad)
+    flash, slab = run(True), run(False)
+    for name, f, s, r in zip(('out', 'dK', 'dQ', 'dV'), flash, slab, ref):
+        bound = 3e-2 * max(1.0, r.abs().max().item())
+        assert (f - r).abs().max().item() <= bound, (name, 'flash vs fp32', (f - r).abs().max().item(), bound)
+        assert (s - r).abs().max().item() <= bound, (name, 'slab vs fp32', (s - r).abs().max().item(), bound)
+
+
+def test_attention_backward_harness_emulated_ranks(cuda_device):
+    """Backward kernels incl. the fused reduce-scatter with emulated ranks (csrc/tests/attn_harness.cu, mode bwd)."""
+    exe = os.path.join(ROOT, 'build', 'attn_harness')
+    if not os.path.exists(exe):
+        subprocess.check_call(['python', os.path.join(ROOT, 'build.py'), 'harness'], cwd=ROOT)
+    r = subprocess.run([exe, 'bwd'], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
+    tail = '\n'.join(r.stdout.splitlines()[-20:])
+    assert r.returncode == 0, tail
+    assert 'fail=0' in r.stdout, tail

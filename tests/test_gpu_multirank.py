@@ -92,3 +92,46 @@ def test_module_multi_gpu(world):
     if _ngpu() < world:
         pytest.skip('needs %d GPUs' % world)
     run_distributed(_module, world, use_cuda=True, timeout=150)
+
+
+def _module_flash(rank, world):
+    """bf16 layer: the slab-free kernels (fused all-gather of q / v, fused reduce-scatter of dq / dv) against the
+    slab path of the same layer on the same inputs, training and inference, two steps (workspace parities)."""
+    import distributed_dot_product.ops.attention as att
+    from distributed_dot_product.module import DistributedDotProductAttn
+    from distributed_dot_product.parallel import broadcast_parameters
+    from distributed_dot_product.parallel.runtime import check_status
+    dev = torch.device('cuda', torch.cuda.current_device())
+    torch.manual_seed(5 + rank)
+    dim, tn, heads = 512, 320, 8
+    model = DistributedDotProductAttn(dim, num_heads=heads, add_bias=True, offset=64).to(dev).to(torch.bfloat16)
+    broadcast_parameters(model)
+    t = tn * world
+    mask = torch.rand(1, tn, t, device=dev) < 0.25
+
+    def run(flash, x):
+        att.FLASH_TRAIN = att.FLASH_FWD = flash
+        xx = x.clone().requires_grad_(True)
+        model.zero_grad()
+        out = model(xx, xx, xx, mask)
+        out.float().pow(2).mean().backward()
+        with torch.no_grad():
+            inf = model(x, x, x, mask)
+        return [out.detach().float(), inf.float(), xx.grad.float()] + [p.grad.float().clone() for p in model.parameters()]
+
+    for step in range(2):
+        x = torch.randn(1, tn, dim, device=dev).to(torch.bfloat16)
+        got, want = run(True, x), run(False, x)
+        check_status()
+        for i, (a, b) in enumerate(zip(got, want)):
+            err = (a - b).abs().max().item()
+            bound = 4e-2 * max(b.abs().max().item(), 1e-3)
+            assert err <= bound, (step, i, err, bound)
+    att.FLASH_TRAIN = att.FLASH_FWD = True
+
+
+@pytest.mark.parametrize('world', [2, 4, 8])
+def test_module_flash_multi_gpu(world):
+    if _ngpu() < world:
+        pytest.skip('needs %d GPUs' % world)
+    run_distributed(_module_flash, world, use_cuda=True, timeout=150)
