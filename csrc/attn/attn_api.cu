@@ -317,35 +317,84 @@ static ColsLayout cols_layout(const ddp_tensor* B, const ddp_tensor* V, int worl
   return L;
 }
 
-// bits_t[b1][cols][ld_words]: bit (r & 31) of word r >> 5 <- mask[b1][r][col] != 0; bits past `rows` are set.
-__global__ void pack_mask_t_kernel(const uint8_t* __restrict__ mask, long long b1, long long rows, long long cols,
-                                   long long m_ld, long long m_sb1, uint32_t* __restrict__ bits, long long ld_words) {
+// Bit-packed masks of the attention kernels, in a layout whose loads coalesce: the kernels' threads own one row
+// (row-side kernels) or one column (column-side kernel) each and read one 32-bit word per 32 elements of the
+// other axis, so the words of 32 neighbouring rows (columns) are interleaved:
+//   plain:      bits[b1][ceil(rows/32)][ld_words][32]   word w of row r   at ((r >> 5) * ld_words + w) * 32 + (r & 31)
+//               bit k of that word <- mask[b1][r][32 w + k] != 0
+//   transposed: bits[b1][ceil(cols/32)][ld_words][32]   word w of column c at ((c >> 5) * ld_words + w) * 32 + (c & 31)
+//               bit k of that word <- mask[b1][32 w + k][c] != 0
+// Elements outside the mask are packed as "masked".
+__global__ void pack_mask_il_kernel(const uint8_t* __restrict__ mask, long long b1, long long rows, long long cols,
+                                    long long m_ld, long long m_sb1, uint32_t* __restrict__ bits, long long ld_words,
+                                    int transposed) {
   const long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
-  const long long per_b = ld_words * cols;
-  if (idx >= b1 * per_b) return;
-  const long long b1i = idx / per_b;
-  const long long r = idx - b1i * per_b;
-  const long long w = r / cols, col = r - w * cols;  // adjacent threads -> adjacent columns (coalesced reads)
-  const uint8_t* src = mask + b1i * m_sb1 + col;
-  uint32_t word = 0;
-  for (int k = 0; k < 32; ++k) {
-    const long long row = w * 32 + k;
-    if (row >= rows || src[row * m_ld] != 0) word |= 1u << k;
+  if (!transposed) {
+    const long long rows_p = (rows + 31) / 32 * 32;
+    if (idx >= b1 * rows_p * ld_words) return;
+    const long long w = idx % ld_words;  // adjacent threads -> adjacent words of one row (coalesced mask reads)
+    long long r = idx / ld_words;
+    const long long b1i = r / rows_p;
+    r -= b1i * rows_p;
+    uint32_t word = 0xffffffffu;
+    if (r < rows) {
+      const uint8_t* src = mask + b1i * m_sb1 + r * m_ld + w * 32;
+      word = 0;
+      if (w * 32 + 32 <= cols && (reinterpret_cast<uintptr_t>(src) & 15) == 0) {
+        const uint4 x = *reinterpret_cast<const uint4*>(src);
+        const uint4 y = *reinterpret_cast<const uint4*>(src + 16);
+        const uint32_t v[8] = {x.x, x.y, x.z, x.w, y.x, y.y, y.z, y.w};
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            if ((v[i] >> (8 * k)) & 0xffu) word |= 1u << (4 * i + k);
+      } else {
+        for (int k = 0; k < 32; ++k) {
+          const long long c = w * 32 + k;
+          if (c >= cols || src[k] != 0) word |= 1u << k;
+        }
+      }
+    }
+    bits[(b1i * (rows_p / 32) + (r >> 5)) * ld_words * 32 + w * 32 + (r & 31)] = word;
+  } else {
+    const long long cols_p = (cols + 31) / 32 * 32;
+    if (idx >= b1 * cols_p * ld_words) return;
+    const long long c = idx % cols_p;  // adjacent threads -> adjacent columns (coalesced mask reads)
+    long long r = idx / cols_p;
+    const long long w = r % ld_words;
+    const long long b1i = r / ld_words;
+    uint32_t word = 0xffffffffu;
+    if (c < cols) {
+      const uint8_t* src = mask + b1i * m_sb1 + c;
+      word = 0;
+      for (int k = 0; k < 32; ++k) {
+        const long long row = w * 32 + k;
+        if (row >= rows || src[row * m_ld] != 0) word |= 1u << k;
+      }
+    }
+    bits[(b1i * (cols_p / 32) + (c >> 5)) * ld_words * 32 + w * 32 + (c & 31)] = word;
   }
-  bits[(b1i * cols + col) * ld_words + w] = word;
 }
 
 }  // namespace ddp
 
-extern "C" int ddp_pack_mask_t(const uint8_t* mask, int64_t b1, int64_t rows, int64_t cols, int64_t mask_ld,
-                               int64_t mask_sb1, uint32_t* bits_t, int64_t ld_words, void* stream) {
-  const long long total = b1 * cols * ld_words;
+extern "C" size_t ddp_attn_mask_words(int64_t b1, int64_t rows, int64_t cols, int transposed) {
+  const int64_t own = transposed ? cols : rows, other = transposed ? rows : cols;
+  return (size_t)b1 * (size_t)((own + 31) / 32) * (size_t)((other + 31) / 32) * 32;
+}
+
+extern "C" int ddp_attn_pack_mask(const uint8_t* mask, int64_t b1, int64_t rows, int64_t cols, int64_t mask_ld,
+                                  int64_t mask_sb1, uint32_t* bits, int transposed, void* stream) {
+  const long long own = transposed ? cols : rows, other = transposed ? rows : cols;
+  const long long ld_words = (other + 31) / 32;
+  const long long total = b1 * ((own + 31) / 32 * 32) * ld_words;
   if (total <= 0) return 0;
   const int threads = 256;
   const long long blocks = (total + threads - 1) / threads;
-  ddp::pack_mask_t_kernel<<<static_cast<unsigned>(blocks), threads, 0, static_cast<cudaStream_t>(stream)>>>(
-      mask, b1, rows, cols, mask_ld, mask_sb1, bits_t, ld_words);
-  return ddp::cuda_check(cudaGetLastError(), "pack_mask_t launch");
+  ddp::pack_mask_il_kernel<<<static_cast<unsigned>(blocks), threads, 0, static_cast<cudaStream_t>(stream)>>>(
+      mask, b1, rows, cols, mask_ld, mask_sb1, bits, ld_words, transposed);
+  return ddp::cuda_check(cudaGetLastError(), "attn_pack_mask launch");
 }
 
 extern "C" int ddp_attn_bwd_cols_workspace(const ddp_tensor* B, const ddp_tensor* V, int world, int chunk_rows,

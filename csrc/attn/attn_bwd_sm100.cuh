@@ -63,11 +63,11 @@ struct alignas(64) AttnBwdParams {
   int dbg;
 };
 
-// All-gather pusher shared by the backward kernels: warps 2-3 of every CTA copy this rank's B and V in chunks
+// All-gather pusher shared by the backward kernels: warp 2 of every CTA copies this rank's B and V in chunks
 // into every peer's workspace and publish one flag per (operand, batch entry, chunk).
-__device__ __forceinline__ void attn_push_gather(const AttnBwdParams& p, int Bt, int warp2, int lane) {
-  const int gw = blockIdx.x * 2 + warp2;
-  const int gstride = gridDim.x * 2;
+__device__ __forceinline__ void attn_push_gather(const AttnBwdParams& p, int Bt, int lane) {
+  const int gw = blockIdx.x;
+  const int gstride = gridDim.x;
   const int per_which = Bt * p.n_chunks;
   const int n_items = 2 * per_which;
   if (gw < n_items) {
@@ -204,10 +204,10 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd_rows_kernel(const __gr
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(&kv_full[s], 1);
-      mbar_init(&kv_empty[s], 1);
+      mbar_init(&kv_empty[s], 2);  // one arrival per MMA issuer
     }
     mbar_init(a_full, 1);
-    mbar_init(a_empty, 1);
+    mbar_init(a_empty, 2);
     for (int w = 0; w < 2; ++w) {
       mbar_init(&s_full[w], 1);
       mbar_init(&s_empty[w], 8);
@@ -280,67 +280,62 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd_rows_kernel(const __gr
           }
         }
       }
-    } else if (warp == 1) {
-      // ===================================================== MMA issuer (event driven)
+    } else if (warp == 1 || warp == 3) {
+      // ===================================================== MMA issuers (event driven): warp 1 -> w = 0, warp 3 -> w = 1
       if (lane == 0) {
         constexpr uint32_t kIdS = umma_idesc(DT, 0u, 0u, kAtBM, kAbStep);  // S, dP: A K-major, B K-major, N = 64
         constexpr uint32_t kIdA = umma_idesc(DT, 0u, 1u, kAtBM, 64);       // dA: A = dS K-major, B = B_j MN-major
-        uint32_t a_ph = 0;
-        uint32_t se_ph[2] = {0u, 0u}, pf_ph[2] = {0u, 0u};
-        const uint32_t sA_u = smem_u32(sA), sG_u = smem_u32(sG), sDS_u = smem_u32(sDS), sKV_u = smem_u32(sKV);
+        const int w = (warp == 1) ? 0 : 1;
+        uint32_t a_ph = 0, se_ph = 0, pf_ph = 0;
+        const uint32_t sKV_u = smem_u32(sKV);
+        const uint32_t tS_w = tmem_base + w * 64, tP_w = tmem_base + 128 + w * 64, tA_w = tmem_base + 256 + w * 64;
+        uint64_t dA[4], dG[4], dD[4];  // the operands that do not move: A_w, dO_w, dS_w (4 k-slices each)
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk) {
+          dA[kk] = umma_smem_desc(smem_u32(sA) + w * kAtTile + kk * 32, 16, 1024);
+          dG[kk] = umma_smem_desc(smem_u32(sG) + w * kAtTile + kk * 32, 16, 1024);
+          dD[kk] = umma_smem_desc(smem_u32(sDS) + w * kAtTile + kk * 32, 16, 1024);
+        }
         uint32_t g0 = 0;
         for (int it = blockIdx.x; it < items; it += gridDim.x) {
           mbar_wait(a_full, a_ph, 24);
           a_ph ^= 1;
           tc_fence_after();
-          int nS[2] = {0, 0}, nPV[2] = {0, 0};
-          int kvr = 0, released = 0;
+          int nS = 0, nPV = 0, kvr = 0;
           uint32_t spins = 0;
           uint64_t t0 = 0;
-          while (released < nj) {
+          while (nPV < nj) {
             bool progress = false;
-#pragma unroll
-            for (int w = 0; w < 2; ++w) {
-              if (nS[w] < nj) {
-                const int j = nS[w];
-                const uint32_t g = g0 + j;
-                if (j >= kvr && mbar_try_wait(&kv_full[g % STAGES], (g / STAGES) & 1)) kvr = j + 1;
-                if (j < kvr && mbar_try_wait(&s_empty[w], se_ph[w] ^ 1)) {
-                  se_ph[w] ^= 1;
-                  tc_fence_after();
-                  const uint32_t sb = sKV_u + (g % STAGES) * kStage;
-#pragma unroll
-                  for (int kk = 0; kk < 4; ++kk)
-                    umma_ss<false>(tmem_base + w * 64, umma_smem_desc(sA_u + w * kAtTile + kk * 32, 16, 1024),
-                                   umma_smem_desc(sb + kk * 32, 16, 1024), kIdS, kk != 0 ? 1u : 0u);
-#pragma unroll
-                  for (int kk = 0; kk < 4; ++kk)
-                    umma_ss<false>(tmem_base + 128 + w * 64, umma_smem_desc(sG_u + w * kAtTile + kk * 32, 16, 1024),
-                                   umma_smem_desc(sb + kAbHalfTile + kk * 32, 16, 1024), kIdS, kk != 0 ? 1u : 0u);
-                  umma_commit(&s_full[w]);
-                  nS[w] = j + 1;
-                  progress = true;
-                }
-              }
-              if (nPV[w] < nS[w] && mbar_try_wait(&p_full[w], pf_ph[w])) {
-                pf_ph[w] ^= 1;
+            if (nS < nj) {
+              const uint32_t g = g0 + nS;
+              if (nS >= kvr && mbar_try_wait(&kv_full[g % STAGES], (g / STAGES) & 1)) kvr = nS + 1;
+              if (nS < kvr && mbar_try_wait(&s_empty[w], se_ph ^ 1)) {
+                se_ph ^= 1;
                 tc_fence_after();
-                const int j = nPV[w];
-                const uint32_t g = g0 + j;
-                const uint32_t sb = sKV_u + (g % STAGES) * kStage;  // B_j as [K = j][N = d], MN-major
+                const uint64_t db = umma_smem_desc(sKV_u + (g % STAGES) * kStage, 16, 1024);
+                const uint64_t dv = umma_smem_desc(sKV_u + (g % STAGES) * kStage + kAbHalfTile, 16, 1024);
 #pragma unroll
-                for (int kk = 0; kk < 4; ++kk)
-                  umma_ss<false>(tmem_base + 256 + w * 64, umma_smem_desc(sDS_u + w * kAtTile + kk * 32, 16, 1024),
-                                 umma_smem_desc(sb + kk * 2048, kAbHalfTile, 1024, 2), kIdA, (j | kk) != 0 ? 1u : 0u);
-                umma_commit(&o_done[w]);
-                nPV[w] = j + 1;
+                for (int kk = 0; kk < 4; ++kk) umma_ss<false>(tS_w, dA[kk], db + 2 * kk, kIdS, kk != 0 ? 1u : 0u);
+#pragma unroll
+                for (int kk = 0; kk < 4; ++kk) umma_ss<false>(tP_w, dG[kk], dv + 2 * kk, kIdS, kk != 0 ? 1u : 0u);
+                umma_commit(&s_full[w]);
+                ++nS;
                 progress = true;
               }
             }
-            const int lo = min(nPV[0], nPV[1]);
-            while (released < lo) {
-              umma_commit(&kv_empty[(g0 + released) % STAGES]);
-              ++released;
+            if (nPV < nS && mbar_try_wait(&p_full[w], pf_ph)) {
+              pf_ph ^= 1;
+              tc_fence_after();
+              const uint32_t g = g0 + nPV;
+              // B_j as [K = j][N = d], MN-major
+              const uint64_t db = umma_smem_desc(sKV_u + (g % STAGES) * kStage, kAbHalfTile, 1024, 2);
+#pragma unroll
+              for (int kk = 0; kk < 4; ++kk)
+                umma_ss<false>(tA_w, dD[kk], db + 128 * kk, kIdA, (nPV | kk) != 0 ? 1u : 0u);
+              umma_commit(&o_done[w]);
+              umma_commit(&kv_empty[g % STAGES]);  // one of the two arrivals that free the ring slot
+              ++nPV;
+              progress = true;
             }
             if (attn_issuer_watchdog(progress, spins, t0, 26u)) break;
           }
@@ -349,7 +344,7 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd_rows_kernel(const __gr
         }
       }
     } else {
-      if (dist && do_produce) attn_push_gather(p, Bt, warp - 2, lane);
+      if (dist && do_produce) attn_push_gather(p, Bt, lane);  // warp 2
     }
   } else {
     setmaxnreg_inc<kAtRegsHigh>();
@@ -378,15 +373,25 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd_rows_kernel(const __gr
       const float neg_lse = p.neg_lse[static_cast<size_t>(b) * p.stat_ld + row_c];
       const float nds = p.nds[static_cast<size_t>(b) * p.stat_ld + row_c];
       const uint32_t* mrow = nullptr;
-      if (p.mask_bits != nullptr) mrow = p.mask_bits + b1i * p.mb_sb1 + static_cast<long long>(row_c) * p.mb_ld;
-      int j = 0;
-      for (int si = 0; si < p.world; ++si) {
+      if (p.mask_bits != nullptr)  // interleaved layout: the 32 rows of a warp read consecutive words
+        mrow = p.mask_bits + b1i * p.mb_sb1 + static_cast<long long>(row_c >> 5) * p.mb_ld * 32 + (row_c & 31);
+      // mask word of this row for the 32 columns of step jj, fetched one step ahead (see the forward kernel)
+      auto mask_word = [&](int jj) -> uint32_t {
+        if (mrow == nullptr || jj >= nj) return 0u;
+        const int si = jj / p.n_steps, nb = jj - si * p.n_steps;
         const int seg = (p.rank + si) % p.world;
-        for (int nb = 0; nb < p.n_steps; ++nb, ++j) {
+        const int n0 = nb * kAbStep + h * 32;
+        if (p.Tn - n0 <= 0) return 0u;
+        return __ldg(mrow + ((static_cast<long long>(seg) * p.Tn + n0) >> 5) * 32);
+      };
+      uint32_t mk_next = mask_word(0);
+      for (int j = 0; j < nj; ++j) {
+        {
+          const int nb = j % p.n_steps;
           const int n0 = nb * kAbStep + h * 32;
           const int nvalid = max(0, min(32, p.Tn - n0));
-          uint32_t mk = 0u;
-          if (mrow != nullptr && nvalid > 0) mk = __ldg(mrow + ((static_cast<long long>(seg) * p.Tn + n0) >> 5));
+          uint32_t mk = mk_next;
+          mk_next = mask_word(j + 1);
           if (nvalid < 32) mk |= (nvalid <= 0) ? 0xffffffffu : (0xffffffffu << nvalid);
           mbar_wait(&s_full[w], sf_ph, 27);
           sf_ph ^= 1;
@@ -549,10 +554,10 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd_cols_kernel(const __gr
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(&kv_full[s], 1);
-      mbar_init(&kv_empty[s], 1);
+      mbar_init(&kv_empty[s], 2);  // one arrival per MMA issuer
     }
     mbar_init(a_full, 1);
-    mbar_init(a_empty, 1);
+    mbar_init(a_empty, 2);
     for (int w = 0; w < 2; ++w) {
       mbar_init(&s_full[w], 1);
       mbar_init(&s_empty[w], 8);
@@ -627,73 +632,67 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd_cols_kernel(const __gr
           }
         }
       }
-    } else if (warp == 1) {
-      // ===================================================== MMA issuer (event driven)
+    } else if (warp == 1 || warp == 3) {
+      // ===================================================== MMA issuers (event driven): warp 1 -> w = 0, warp 3 -> w = 1
       if (lane == 0) {
         constexpr uint32_t kIdS = umma_idesc(DT, 0u, 0u, kAtBM, kAbStep);  // S^T, dP^T
         constexpr uint32_t kIdO = umma_idesc(DT, 0u, 1u, kAtBM, 64);       // dV, dB: B operand MN-major
-        uint32_t a_ph = 0;
-        uint32_t se_ph[2] = {0u, 0u}, pf_ph[2] = {0u, 0u};
-        const uint32_t sB_u = smem_u32(sB), sV_u = smem_u32(sV), sPt_u = smem_u32(sPt), sDt_u = smem_u32(sDt),
-                       sKV_u = smem_u32(sKV);
+        const int w = (warp == 1) ? 0 : 1;
+        uint32_t a_ph = 0, se_ph = 0, pf_ph = 0;
+        const uint32_t sKV_u = smem_u32(sKV);
+        const uint32_t tS_w = tmem_base + w * 64, tP_w = tmem_base + 128 + w * 64, tV_w = tmem_base + 256 + w * 64,
+                       tB_w = tmem_base + 384 + w * 64;
+        uint64_t dB_[4], dV_[4], dPt[4], dDt[4];  // the operands that do not move (4 k-slices each)
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk) {
+          dB_[kk] = umma_smem_desc(smem_u32(sB) + w * kAtTile + kk * 32, 16, 1024);
+          dV_[kk] = umma_smem_desc(smem_u32(sV) + w * kAtTile + kk * 32, 16, 1024);
+          dPt[kk] = umma_smem_desc(smem_u32(sPt) + w * kAtTile + kk * 32, 16, 1024);
+          dDt[kk] = umma_smem_desc(smem_u32(sDt) + w * kAtTile + kk * 32, 16, 1024);
+        }
         uint32_t g0 = 0;
         for (int it = blockIdx.x; it < items; it += gridDim.x) {
           mbar_wait(a_full, a_ph, 34);
           a_ph ^= 1;
           tc_fence_after();
-          int nS[2] = {0, 0}, nPV[2] = {0, 0};
-          int kvr = 0, released = 0;
+          int nS = 0, nPV = 0, kvr = 0;
           uint32_t spins = 0;
           uint64_t t0 = 0;
-          while (released < nj) {
+          while (nPV < nj) {
             bool progress = false;
-#pragma unroll
-            for (int w = 0; w < 2; ++w) {
-              if (nS[w] < nj) {
-                const int j = nS[w];
-                const uint32_t g = g0 + j;
-                if (j >= kvr && mbar_try_wait(&kv_full[g % STAGES], (g / STAGES) & 1)) kvr = j + 1;
-                if (j < kvr && mbar_try_wait(&s_empty[w], se_ph[w] ^ 1)) {
-                  se_ph[w] ^= 1;
-                  tc_fence_after();
-                  const uint32_t sb = sKV_u + (g % STAGES) * kAbColsStage;
-#pragma unroll
-                  for (int kk = 0; kk < 4; ++kk)
-                    umma_ss<false>(tmem_base + w * 64, umma_smem_desc(sB_u + w * kAtTile + kk * 32, 16, 1024),
-                                   umma_smem_desc(sb + kk * 32, 16, 1024), kIdS, kk != 0 ? 1u : 0u);
-#pragma unroll
-                  for (int kk = 0; kk < 4; ++kk)
-                    umma_ss<false>(tmem_base + 128 + w * 64, umma_smem_desc(sV_u + w * kAtTile + kk * 32, 16, 1024),
-                                   umma_smem_desc(sb + kAbHalfTile + kk * 32, 16, 1024), kIdS, kk != 0 ? 1u : 0u);
-                  umma_commit(&s_full[w]);
-                  nS[w] = j + 1;
-                  progress = true;
-                }
-              }
-              if (nPV[w] < nS[w] && mbar_try_wait(&p_full[w], pf_ph[w])) {
-                pf_ph[w] ^= 1;
+            if (nS < nj) {
+              const uint32_t g = g0 + nS;
+              if (nS >= kvr && mbar_try_wait(&kv_full[g % STAGES], (g / STAGES) & 1)) kvr = nS + 1;
+              if (nS < kvr && mbar_try_wait(&s_empty[w], se_ph ^ 1)) {
+                se_ph ^= 1;
                 tc_fence_after();
-                const int j = nPV[w];
-                const uint32_t g = g0 + j;
-                const uint32_t sb = sKV_u + (g % STAGES) * kAbColsStage;
+                const uint64_t da = umma_smem_desc(sKV_u + (g % STAGES) * kAbColsStage, 16, 1024);
+                const uint64_t dg = umma_smem_desc(sKV_u + (g % STAGES) * kAbColsStage + kAbHalfTile, 16, 1024);
 #pragma unroll
-                for (int kk = 0; kk < 4; ++kk)  // dV_w += P^T_w dO_i
-                  umma_ss<false>(tmem_base + 256 + w * 64, umma_smem_desc(sPt_u + w * kAtTile + kk * 32, 16, 1024),
-                                 umma_smem_desc(sb + kAbHalfTile + kk * 2048, kAbHalfTile, 1024, 2), kIdO,
-                                 (j | kk) != 0 ? 1u : 0u);
+                for (int kk = 0; kk < 4; ++kk) umma_ss<false>(tS_w, dB_[kk], da + 2 * kk, kIdS, kk != 0 ? 1u : 0u);
 #pragma unroll
-                for (int kk = 0; kk < 4; ++kk)  // dB_w += dS^T_w A_i
-                  umma_ss<false>(tmem_base + 384 + w * 64, umma_smem_desc(sDt_u + w * kAtTile + kk * 32, 16, 1024),
-                                 umma_smem_desc(sb + kk * 2048, kAbHalfTile, 1024, 2), kIdO, (j | kk) != 0 ? 1u : 0u);
-                umma_commit(&o_done[w]);
-                nPV[w] = j + 1;
+                for (int kk = 0; kk < 4; ++kk) umma_ss<false>(tP_w, dV_[kk], dg + 2 * kk, kIdS, kk != 0 ? 1u : 0u);
+                umma_commit(&s_full[w]);
+                ++nS;
                 progress = true;
               }
             }
-            const int lo = min(nPV[0], nPV[1]);
-            while (released < lo) {
-              umma_commit(&kv_empty[(g0 + released) % STAGES]);
-              ++released;
+            if (nPV < nS && mbar_try_wait(&p_full[w], pf_ph)) {
+              pf_ph ^= 1;
+              tc_fence_after();
+              const uint32_t g = g0 + nPV;
+              const uint64_t da = umma_smem_desc(sKV_u + (g % STAGES) * kAbColsStage, kAbHalfTile, 1024, 2);
+              const uint64_t dg = umma_smem_desc(sKV_u + (g % STAGES) * kAbColsStage + kAbHalfTile, kAbHalfTile, 1024, 2);
+#pragma unroll
+              for (int kk = 0; kk < 4; ++kk)  // dV_w += P^T_w dO_i
+                umma_ss<false>(tV_w, dPt[kk], dg + 128 * kk, kIdO, (nPV | kk) != 0 ? 1u : 0u);
+#pragma unroll
+              for (int kk = 0; kk < 4; ++kk)  // dB_w += dS^T_w A_i
+                umma_ss<false>(tB_w, dDt[kk], da + 128 * kk, kIdO, (nPV | kk) != 0 ? 1u : 0u);
+              umma_commit(&o_done[w]);
+              umma_commit(&kv_empty[g % STAGES]);  // one of the two arrivals that free the ring slot
+              ++nPV;
+              progress = true;
             }
             if (attn_issuer_watchdog(progress, spins, t0, 36u)) break;
           }
@@ -702,7 +701,7 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd_cols_kernel(const __gr
         }
       }
     } else {
-      if (dist && do_push) attn_push_gather(p, Bt, warp - 2, lane);
+      if (dist && do_push) attn_push_gather(p, Bt, lane);  // warp 2
     }
   } else {
     setmaxnreg_inc<kAtRegsHigh>();
@@ -729,14 +728,22 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd_cols_kernel(const __gr
       const int col0 = c0 + w * kAtBM + q * 32;  // first column (row of B / V within the segment) of this warp
       const int col = col0 + lane;
       const uint32_t* mrow = nullptr;
-      if (p.mask_bits != nullptr)
-        mrow = p.mask_bits + b1i * p.mb_sb1 +
-               (static_cast<long long>(seg) * p.Tn + min(col, p.Tn - 1)) * p.mb_ld;
+      if (p.mask_bits != nullptr) {  // transposed + interleaved: the 32 columns of a warp read consecutive words
+        const long long cg = static_cast<long long>(seg) * p.Tn + min(col, p.Tn - 1);
+        mrow = p.mask_bits + b1i * p.mb_sb1 + (cg >> 5) * p.mb_ld * 32 + (cg & 31);
+      }
+      auto mask_word = [&](int jj) -> uint32_t {  // transposed mask: 32 rows of step jj, one step ahead
+        if (mrow == nullptr || jj >= nj) return 0u;
+        const int i0 = jj * kAbStep + h * 32;
+        if (p.M - i0 <= 0) return 0u;
+        return __ldg(mrow + (i0 >> 5) * 32);
+      };
+      uint32_t mk_next = mask_word(0);
       for (int j = 0; j < nj; ++j, ++g) {
         const int i0 = j * kAbStep + h * 32;
         const int nvalid = max(0, min(32, p.M - i0));
-        uint32_t mk = 0u;
-        if (mrow != nullptr && nvalid > 0) mk = __ldg(mrow + (i0 >> 5));
+        uint32_t mk = mk_next;
+        mk_next = mask_word(j + 1);
         if (nvalid < 32) mk |= (nvalid <= 0) ? 0xffffffffu : (0xffffffffu << nvalid);
         const uint32_t slot = g % STAGES;
         mbar_wait(&kv_full[slot], (g / STAGES) & 1, 37);  // the row statistics of the step (TMA -> our loads)

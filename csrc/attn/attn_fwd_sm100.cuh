@@ -9,10 +9,10 @@
 //
 //   warp 0      TMA producer: A tiles (two 128-row blocks per work item) and a ring of (B_j, V_j) column blocks;
 //               polls the peers' per-chunk flags before touching gathered rows
-//   warp 1      MMA issuer:   S_w = A_w . B_j^T (128x128, K = d) for the two row blocks w = 0, 1 and, per row block,
+//   warps 1, 3  MMA issuers (one per row block w):   S_w = A_w . B_j^T (128x128, K = d) for the two row blocks w = 0, 1 and, per row block,
 //               TWO independent accumulators O_{w,h} += P_w[:, half h] . V_j[half h] (128 x dv, K = 64); event
 //               driven, so S_w(j+1) is computed while the softmax warps are still busy with step j
-//   warps 2-3   TMEM alloc; all-gather pushers (B and V chunks -> every peer's workspace, one flag per chunk)
+//   warp 2      TMEM alloc; all-gather pusher (B and V chunks -> every peer's workspace, one flag per chunk)
 //   warps 4-19  softmax: warp = (row block w, column half h, lane quadrant q), thread = one row x 64 columns held
 //               in registers.  Every (row, half) is its own online-softmax stream (own running max and sum, own
 //               O accumulator), so no per-step exchange between the two threads of a row is needed; the two
@@ -114,10 +114,10 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_fwd_kernel(const __grid_co
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(&kv_full[s], 1);
-      mbar_init(&kv_empty[s], 1);
+      mbar_init(&kv_empty[s], 2);  // one arrival per MMA issuer
     }
     mbar_init(a_full, 1);
-    mbar_init(a_empty, 1);
+    mbar_init(a_empty, 2);
     for (int w = 0; w < 2; ++w) {
       mbar_init(&s_full[w], 1);
       mbar_init(&s_empty[w], 8);
@@ -203,70 +203,75 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_fwd_kernel(const __grid_co
         }
       }
     }
-  } else if (warp == 1) {
-    // ======================================================= MMA issuer (event driven)
-    // A softmax warpgroup releases S_w as soon as the row sits in its registers, so S_w(j+1) is computed while
-    // the warpgroup still works on step j; the single issuing thread therefore polls the four conditions
-    // (S_w buffer free + operands landed, P_w staged; w = 0, 1) and issues whatever has become possible.
+  } else if (warp == 1 || warp == 3) {
+    // ======================================================= MMA issuers (event driven), one per row block
+    // A softmax warp releases S_w as soon as its values sit in registers, so S_w(j+1) is computed while the
+    // exponentials of step j are still running; the issuing thread polls its three conditions (S_w buffer free +
+    // operands landed; half h of P_w staged, h = 0, 1) and issues whatever has become possible.  One issuing
+    // thread for BOTH row blocks was the bottleneck of this kernel (~30 dependent instructions per tcgen05.mma,
+    // 24 MMAs per step): warp 1 serves row block 0, warp 3 row block 1.
     if (lane == 0) {
       constexpr uint32_t kIdS = umma_idesc(DT, 0u, 0u, kAtBM, kAtBN);  // A K-major, B K-major
       constexpr uint32_t kIdO = umma_idesc(DT, 0u, 1u, kAtBM, 64);     // A = P K-major, B = V MN-major
-      uint32_t a_ph = 0;
-      uint32_t se_ph[2] = {0u, 0u}, pf_ph[4] = {0u, 0u, 0u, 0u};
-      const uint32_t sA_u = smem_u32(sA), sP_u = smem_u32(sP), sKV_u = smem_u32(sKV);
+      const int w = (warp == 1) ? 0 : 1;
+      uint32_t a_ph = 0, se_ph = 0, pf_ph[2] = {0u, 0u};
+      const uint32_t sKV_u = smem_u32(sKV);
+      const uint32_t tS_w = tmem_base + w * kAtBN;
+      const uint32_t tO_w = tmem_base + 2 * kAtBN + w * 128;
+      // descriptors of the operands that do not move: A_w (4 k-slices) and the two halves of P_w (4 k-slices each)
+      uint64_t dA[4], dP[2][4];
+#pragma unroll
+      for (int kk = 0; kk < 4; ++kk) {
+        dA[kk] = umma_smem_desc(smem_u32(sA) + w * kAtTile + kk * 32, 16, 1024);
+        dP[0][kk] = umma_smem_desc(smem_u32(sP) + w * kAtPBytes + kk * 32, 16, 1024);
+        dP[1][kk] = umma_smem_desc(smem_u32(sP) + w * kAtPBytes + kAtTile + kk * 32, 16, 1024);
+      }
       uint32_t g0 = 0;  // steps issued by earlier work items: step j of this item uses ring slot (g0 + j) % STAGES
       for (int it = blockIdx.x; it < items; it += gridDim.x) {
         mbar_wait(a_full, a_ph, 14);
         a_ph ^= 1;
         tc_fence_after();
-        int nS[2] = {0, 0}, nPV[4] = {0, 0, 0, 0};
+        int nS = 0, nPV[2] = {0, 0};
         int kvr = 0;       // steps of this item whose operands are known to have landed
-        int released = 0;  // steps whose ring slot went back to the producer
+        int released = 0;  // steps whose ring slot this issuer has handed back
         uint32_t spins = 0;
         uint64_t t0 = 0;
         while (released < nj) {
           bool progress = false;
+          if (nS < nj) {
+            const uint32_t g = g0 + nS;
+            if (nS >= kvr && mbar_try_wait(&kv_full[g % STAGES], (g / STAGES) & 1)) kvr = nS + 1;
+            if (nS < kvr && mbar_try_wait(&s_empty[w], se_ph ^ 1)) {
+              se_ph ^= 1;
+              tc_fence_after();
+              const uint64_t db = umma_smem_desc(sKV_u + (g % STAGES) * kAtStageBytes, 16, 1024);
 #pragma unroll
-          for (int w = 0; w < 2; ++w) {
-            if (nS[w] < nj) {
-              const int j = nS[w];
-              const uint32_t g = g0 + j;
-              if (j >= kvr && mbar_try_wait(&kv_full[g % STAGES], (g / STAGES) & 1)) kvr = j + 1;
-              if (j < kvr && mbar_try_wait(&s_empty[w], se_ph[w] ^ 1)) {
-                se_ph[w] ^= 1;
-                tc_fence_after();
-                const uint32_t sb = sKV_u + (g % STAGES) * kAtStageBytes;
-#pragma unroll
-                for (int kk = 0; kk < 4; ++kk)
-                  umma_ss<false>(tmem_base + w * kAtBN, umma_smem_desc(sA_u + w * kAtTile + kk * 32, 16, 1024),
-                                 umma_smem_desc(sb + kk * 32, 16, 1024), kIdS, kk != 0 ? 1u : 0u);
-                umma_commit(&s_full[w]);
-                nS[w] = j + 1;
-                progress = true;
-              }
-            }
-#pragma unroll
-            for (int h = 0; h < 2; ++h) {
-              const int st = w * 2 + h;
-              if (nPV[st] < nS[w] && mbar_try_wait(&p_full[st], pf_ph[st])) {
-                pf_ph[st] ^= 1;
-                tc_fence_after();
-                const int j = nPV[st];
-                const uint32_t g = g0 + j;
-                const uint32_t sv = sKV_u + (g % STAGES) * kAtStageBytes + kAtTile + h * (4 * 2048);
-                const uint32_t sp = sP_u + w * kAtPBytes + h * kAtTile;
-#pragma unroll
-                for (int kk = 0; kk < 4; ++kk)
-                  umma_ss<false>(tmem_base + 2 * kAtBN + st * 64, umma_smem_desc(sp + kk * 32, 16, 1024),
-                                 umma_smem_desc(sv + kk * 2048, kAtTile, 1024, 2), kIdO, (j | kk) != 0 ? 1u : 0u);
-                umma_commit(&o_done[st]);
-                nPV[st] = j + 1;
-                progress = true;
-              }
+              for (int kk = 0; kk < 4; ++kk) umma_ss<false>(tS_w, dA[kk], db + 2 * kk, kIdS, kk != 0 ? 1u : 0u);
+              umma_commit(&s_full[w]);
+              ++nS;
+              progress = true;
             }
           }
-          // all four streams are through with column block `released`: its ring slot goes back to the producer
-          const int lo = min(min(nPV[0], nPV[1]), min(nPV[2], nPV[3]));
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            if (nPV[h] < nS && mbar_try_wait(&p_full[w * 2 + h], pf_ph[h])) {
+              pf_ph[h] ^= 1;
+              tc_fence_after();
+              const int j = nPV[h];
+              const uint32_t g = g0 + j;
+              const uint64_t dv = umma_smem_desc(
+                  sKV_u + (g % STAGES) * kAtStageBytes + kAtTile + h * (4 * 2048), kAtTile, 1024, 2);
+#pragma unroll
+              for (int kk = 0; kk < 4; ++kk)
+                umma_ss<false>(tO_w + h * 64, dP[h][kk], dv + 128 * kk, kIdO, (j | kk) != 0 ? 1u : 0u);
+              umma_commit(&o_done[w * 2 + h]);
+              nPV[h] = j + 1;
+              progress = true;
+            }
+          }
+          // both streams of this row block are through with column block `released`: one of the two arrivals that
+          // hand its ring slot back to the producer
+          const int lo = min(nPV[0], nPV[1]);
           while (released < lo) {
             umma_commit(&kv_empty[(g0 + released) % STAGES]);
             ++released;
@@ -292,9 +297,9 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_fwd_kernel(const __grid_co
     }
   } else {
     // ======================================================= all-gather pushers (B and V)
-    if (dist && do_produce) {
-      const int gw = blockIdx.x * 2 + (warp - 2);
-      const int gstride = gridDim.x * 2;
+    if (dist && do_produce) {  // warp 2 only (warp 3 is the second MMA issuer)
+      const int gw = blockIdx.x;
+      const int gstride = gridDim.x;
       const int per_which = Bt * p.n_chunks;
       const int n_items = 2 * per_which;
       if (gw < n_items) {
@@ -377,22 +382,32 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_fwd_kernel(const __grid_co
       const int row = row0 + lane;
       const uint32_t* mrow = nullptr;
       if (p.mask_bits != nullptr)
-        mrow = p.mask_bits + b1i * p.mb_sb1 + static_cast<long long>(min(row, p.M - 1)) * p.mb_ld;
+        mrow = p.mask_bits + b1i * p.mb_sb1 + static_cast<long long>(min(row, p.M - 1) >> 5) * p.mb_ld * 32 +
+               (min(row, p.M - 1) & 31);  // interleaved layout: the 32 rows of a warp read consecutive words
       float m_used = -INFINITY, l = 0.f;
-      int j = 0;
-      for (int si = 0; si < p.world; ++si) {
+      // mask words of this row for the 64 columns of step jj (bit set = masked out); fetched ONE STEP AHEAD so
+      // that their L2 latency never sits between the arrival of S and the exponentials
+      auto mask_words = [&](int jj, uint32_t (&o)[2]) {
+        o[0] = 0u;
+        o[1] = 0u;
+        if (mrow == nullptr || jj >= nj) return;
+        const int si = jj / p.n_blocks, nb = jj - si * p.n_blocks;
         const int seg = (p.rank + si) % p.world;
-        for (int nb = 0; nb < p.n_blocks; ++nb, ++j) {
+        const int n0 = nb * kAtBN + h * 64;
+        const int nvalid = p.Tn - n0;
+        const uint32_t* mp = mrow + ((static_cast<long long>(seg) * p.Tn + n0) >> 5) * 32;
+        if (nvalid > 0) o[0] = __ldg(mp);
+        if (nvalid > 32) o[1] = __ldg(mp + 32);
+      };
+      uint32_t mk_next[2];
+      mask_words(0, mk_next);
+      for (int j = 0; j < nj; ++j) {
+        {
+          const int nb = j % p.n_blocks;
           const int n0 = nb * kAtBN + h * 64;                  // first column of this thread's half
           const int nvalid = max(0, min(64, p.Tn - n0));
-          // mask words of this row for the 64 columns (bit set = masked out), fetched before the wait so that
-          // their latency hides behind the MMA
-          uint32_t mk[2] = {0u, 0u};
-          if (mrow != nullptr) {
-            const uint32_t* mp = mrow + ((static_cast<long long>(seg) * p.Tn + n0) >> 5);
-            if (nvalid > 0) mk[0] = __ldg(mp);
-            if (nvalid > 32) mk[1] = __ldg(mp + 1);
-          }
+          uint32_t mk[2] = {mk_next[0], mk_next[1]};
+          mask_words(j + 1, mk_next);
           if (nvalid < 64) {
 #pragma unroll
             for (int i = 0; i < 2; ++i) {

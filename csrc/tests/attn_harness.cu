@@ -141,8 +141,8 @@ static bool run_case(const Case& c, int dbg, bool verbose) {
     if (c.maskmode) {
       CK(cudaMalloc(&dMask[r], mask[r].size()));
       CK(cudaMemcpy(dMask[r], mask[r].data(), mask[r].size(), cudaMemcpyHostToDevice));
-      CK(cudaMalloc(&dBits[r], (size_t)c.b1 * c.M * ldw * 4));
-      if (ddp_pack_mask((const uint8_t*)dMask[r], c.b1, c.M, T, T, (long long)c.M * T, (uint32_t*)dBits[r], ldw, 0)) {
+      CK(cudaMalloc(&dBits[r], ddp_attn_mask_words(c.b1, c.M, T, 0) * 4));
+      if (ddp_attn_pack_mask((const uint8_t*)dMask[r], c.b1, c.M, T, T, (long long)c.M * T, (uint32_t*)dBits[r], 0, 0)) {
         printf("pack_mask failed: %s\n", ddp_last_error());
         return false;
       }
@@ -179,8 +179,8 @@ static bool run_case(const Case& c, int dbg, bool verbose) {
         cm.exit_counter = exitc[r];
         ddp_tensor a = dview(A[r], dA[r], c.dt), b = dview(B[r], dB[r], c.dt), v = dview(V[r], dV[r], c.dt),
                    o = dview(O[r], dO[r], c.dt);
-        int e = ddp_attn_fwd(&a, &b, &v, &o, (float*)dLse[r], (const uint32_t*)dBits[r], ldw, (long long)c.M * ldw, scale,
-                             W > 1 ? &cm : nullptr, dbg, 0);
+        int e = ddp_attn_fwd(&a, &b, &v, &o, (float*)dLse[r], (const uint32_t*)dBits[r], ldw,
+                             (long long)(ddp_attn_mask_words(c.b1, c.M, T, 0) / c.b1), scale, W > 1 ? &cm : nullptr, dbg, 0);
         if (e) {
           printf("  ddp_attn_fwd error %d: %s\n", e, ddp_last_error());
           ok = false;
@@ -404,10 +404,10 @@ static bool run_bwd_case(const Case& c, bool verbose) {
     if (c.maskmode) {
       CK(cudaMalloc(&dMask[r], mask[r].size()));
       CK(cudaMemcpy(dMask[r], mask[r].data(), mask[r].size(), cudaMemcpyHostToDevice));
-      CK(cudaMalloc(&dBits[r], (size_t)c.b1 * c.M * ldw * 4));
-      CK(cudaMalloc(&dBitsT[r], (size_t)c.b1 * T * ldwt * 4));
-      if (ddp_pack_mask((const uint8_t*)dMask[r], c.b1, c.M, T, T, (long long)c.M * T, (uint32_t*)dBits[r], ldw, 0) ||
-          ddp_pack_mask_t((const uint8_t*)dMask[r], c.b1, c.M, T, T, (long long)c.M * T, (uint32_t*)dBitsT[r], ldwt, 0)) {
+      CK(cudaMalloc(&dBits[r], ddp_attn_mask_words(c.b1, c.M, T, 0) * 4));
+      CK(cudaMalloc(&dBitsT[r], ddp_attn_mask_words(c.b1, c.M, T, 1) * 4));
+      if (ddp_attn_pack_mask((const uint8_t*)dMask[r], c.b1, c.M, T, T, (long long)c.M * T, (uint32_t*)dBits[r], 0, 0) ||
+          ddp_attn_pack_mask((const uint8_t*)dMask[r], c.b1, c.M, T, T, (long long)c.M * T, (uint32_t*)dBitsT[r], 1, 0)) {
         printf("pack_mask failed: %s\n", ddp_last_error());
         return false;
       }
@@ -451,10 +451,12 @@ static bool run_bwd_case(const Case& c, bool verbose) {
         int e;
         if (kernel == 0)
           e = ddp_attn_bwd_rows(&a, &g, &b, &v, &oa, (const float*)dNl[r], (const float*)dNd[r], stat_ld,
-                                (const uint32_t*)dBits[r], ldw, (long long)c.M * ldw, scale, W > 1 ? &cm : nullptr, 0, 0);
+                                (const uint32_t*)dBits[r], ldw, (long long)(ddp_attn_mask_words(c.b1, c.M, T, 0) / c.b1), scale,
+                                W > 1 ? &cm : nullptr, 0, 0);
         else
           e = ddp_attn_bwd_cols(&a, &g, &b, &v, &ov, &ob, (const float*)dNl[r], (const float*)dNd[r], stat_ld,
-                                (const uint32_t*)dBitsT[r], ldwt, (long long)T * ldwt, scale, W > 1 ? &cm : nullptr, 0, 0);
+                                (const uint32_t*)dBitsT[r], ldwt, (long long)(ddp_attn_mask_words(c.b1, c.M, T, 1) / c.b1), scale,
+                                W > 1 ? &cm : nullptr, 0, 0);
         if (e) {
           printf("  backward kernel %d error %d: %s\n", kernel, e, ddp_last_error());
           ok = false;
@@ -524,7 +526,7 @@ static bool run_bwd_case(const Case& c, bool verbose) {
   return ok;
 }
 
-static void perf_bwd(int dt, int H, int M, int Tn, int d, int iters) {
+static void perf_bwd(int dt, int H, int M, int Tn, int d, int iters, bool with_mask = false) {
   HT A = make_ht(1, H, M, d, true, false), B = make_ht(1, H, Tn, d, true, false);
   void *dA_, *dB_, *dV_, *dG_, *oA, *oB, *oV;
   float *nl, *nd;
@@ -538,20 +540,26 @@ static void perf_bwd(int dt, int H, int M, int Tn, int d, int iters) {
   ddp_tensor a = dview(A, dA_, dt), g = dview(A, dG_, dt), b = dview(B, dB_, dt), v = dview(B, dV_, dt),
              oa = dview(A, oA, dt), ob = dview(B, oB, dt), ov = dview(B, oV, dt);
   const float scale = 1.0f / sqrtf((float)d);
+  uint32_t *mb = nullptr, *mbt = nullptr;
+  const long long ldw = (Tn + 31) / 32, ldwt = (M + 31) / 32;
+  if (with_mask) {
+    CK(cudaMalloc((void**)&mb, (size_t)M * ldw * 4)); CK(cudaMemset(mb, 0, (size_t)M * ldw * 4));
+    CK(cudaMalloc((void**)&mbt, (size_t)Tn * ldwt * 4)); CK(cudaMemset(mbt, 0, (size_t)Tn * ldwt * 4));
+  }
   cudaEvent_t e0, e1, e2;
   CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1)); CK(cudaEventCreate(&e2));
   for (int i = 0; i < 2; ++i) {
-    if (ddp_attn_bwd_rows(&a, &g, &b, &v, &oa, nl, nd, M, nullptr, 0, 0, scale, nullptr, 0, 0) ||
-        ddp_attn_bwd_cols(&a, &g, &b, &v, &ov, &ob, nl, nd, M, nullptr, 0, 0, scale, nullptr, 0, 0)) {
+    if (ddp_attn_bwd_rows(&a, &g, &b, &v, &oa, nl, nd, M, mb, ldw, (long long)M * ldw, scale, nullptr, 0, 0) ||
+        ddp_attn_bwd_cols(&a, &g, &b, &v, &ov, &ob, nl, nd, M, mbt, ldwt, (long long)Tn * ldwt, scale, nullptr, 0, 0)) {
       printf("perf launch failed: %s\n", ddp_last_error());
       return;
     }
   }
   CK(cudaDeviceSynchronize());
   CK(cudaEventRecord(e0));
-  for (int i = 0; i < iters; ++i) ddp_attn_bwd_rows(&a, &g, &b, &v, &oa, nl, nd, M, nullptr, 0, 0, scale, nullptr, 0, 0);
+  for (int i = 0; i < iters; ++i) ddp_attn_bwd_rows(&a, &g, &b, &v, &oa, nl, nd, M, mb, ldw, (long long)M * ldw, scale, nullptr, 0, 0);
   CK(cudaEventRecord(e1));
-  for (int i = 0; i < iters; ++i) ddp_attn_bwd_cols(&a, &g, &b, &v, &ov, &ob, nl, nd, M, nullptr, 0, 0, scale, nullptr, 0, 0);
+  for (int i = 0; i < iters; ++i) ddp_attn_bwd_cols(&a, &g, &b, &v, &ov, &ob, nl, nd, M, mbt, ldwt, (long long)Tn * ldwt, scale, nullptr, 0, 0);
   CK(cudaEventRecord(e2));
   CK(cudaEventSynchronize(e2));
   float ms_r, ms_c;
@@ -560,8 +568,8 @@ static void perf_bwd(int dt, int H, int M, int Tn, int d, int iters) {
   ms_r /= iters; ms_c /= iters;
   const double tile = 2.0 * H * (double)M * Tn * d;
   const int site = ddp_debug_timeout_site_attn();
-  printf("PERF ATTN-BWD %s H=%d M=%d T=%d d=%d: rows (dA) %.3f ms %.1f TFLOP/s   cols (dB, dV) %.3f ms %.1f TFLOP/s%s\n",
-         dt == DDP_BF16 ? "bf16" : "fp16", H, M, Tn, d, ms_r, 3 * tile / ms_r * 1e-9, ms_c, 4 * tile / ms_c * 1e-9,
+  printf("PERF ATTN-BWD %s H=%d M=%d T=%d d=%d mask=%d: rows (dA) %.3f ms %.1f TFLOP/s   cols (dB, dV) %.3f ms %.1f TFLOP/s%s\n",
+         dt == DDP_BF16 ? "bf16" : "fp16", H, M, Tn, d, (int)with_mask, ms_r, 3 * tile / ms_r * 1e-9, ms_c, 4 * tile / ms_c * 1e-9,
          site ? "  WATCHDOG FIRED" : "");
   fflush(stdout);
 }
@@ -673,7 +681,10 @@ int main(int argc, char** argv) {
     run_bwd_case({bf, 4, 2, 2, 160, 160, 32, 32, true, 2, 64, 0}, true);
     run_bwd_case({bf, 4, 1, 3, 100, 96, 64, 64, false, 1, 32, 0}, true);
     printf("SUMMARY-BWD pass=%d fail=%d\n", g_pass, g_fail);
-    if (mode == "bwdfull") perf_bwd(DDP_BF16, 16, 8192, 8192, 64, 5);
+    if (mode == "bwdfull") {
+      perf_bwd(DDP_BF16, 16, 8192, 8192, 64, 5);
+      perf_bwd(DDP_BF16, 16, 8192, 8192, 64, 5, true);
+    }
     return g_fail ? 1 : 0;
   }
   if (mode == "perf" || mode == "full") {

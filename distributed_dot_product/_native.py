@@ -102,8 +102,10 @@ def load():
                                                     c.POINTER(c.c_size_t)]
         lib.ddp_attn_bwd_cols.argtypes = [tp, tp, tp, tp, tp, tp, c.c_void_p, c.c_void_p, c.c_int64, c.c_void_p,
                                           c.c_int64, c.c_int64, c.c_float, c.POINTER(Comm), c.c_int, c.c_void_p]
-        lib.ddp_pack_mask_t.argtypes = [c.c_void_p, c.c_int64, c.c_int64, c.c_int64, c.c_int64, c.c_int64, c.c_void_p,
-                                        c.c_int64, c.c_void_p]
+        lib.ddp_attn_mask_words.argtypes = [c.c_int64, c.c_int64, c.c_int64, c.c_int]
+        lib.ddp_attn_mask_words.restype = c.c_size_t
+        lib.ddp_attn_pack_mask.argtypes = [c.c_void_p, c.c_int64, c.c_int64, c.c_int64, c.c_int64, c.c_int64, c.c_void_p,
+                                           c.c_int, c.c_void_p]
         lib.ddp_debug_timeout_site.restype = c.c_int
         lib.ddp_debug_timeout_site_rowops.restype = c.c_int
         lib.ddp_read_u32.argtypes = [c.c_void_p, c.POINTER(c.c_uint32)]

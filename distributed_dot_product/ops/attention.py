@@ -123,7 +123,7 @@ def flash_attention_forward(k4, q4, v4, mask, scale, offset, out4, want_lse=Fals
         if bits is None:
             bits, ldw, sb1w = _pack_mask(mask, b, h, tn, total, k4.device)
         else:
-            ldw, sb1w = bits.size(-1), tn * bits.size(-1)
+            ldw, sb1w = (total + 31) // 32, bits.numel() // b
     lse = torch.empty(b, h, tn, dtype=torch.float32, device=k4.device) if want_lse else None
     va, vb, vv, vo = _g.as_view(k4), _g.as_view(q4), _g.as_view(v4), _g.as_view(out4)
     comm_ptr = None
@@ -144,26 +144,22 @@ def flash_attention_forward(k4, q4, v4, mask, scale, offset, out4, want_lse=Fals
 
 
 def _pack_mask(mask, b, h, tn, total, device, transposed=False):
-    """Bit-packs a bool ``[B, T/N, T]`` mask (True = masked out): along the columns (``[B, T/N, T/32]``) for the
-    row-side kernels, or transposed (``[B, T, ceil(T/N / 32)]``, bits along the rows) for the column-side one."""
+    """Bit-packs a bool ``[B, T/N, T]`` mask (True = masked out) for the attention kernels
+    (``ddp_attn_pack_mask``): one word per 32 columns of a row for the row-side kernels, or - ``transposed`` - per
+    32 rows of a column for the column-side kernel, words of 32 neighbouring rows (columns) interleaved so that a
+    warp's loads coalesce.  Returns ``(bits, ld_words, words_per_batch_entry)``."""
     import ctypes
     from distributed_dot_product.ops.softmax import _prep_mask
     lib = _native.load()
     mu8, m_ld, m_sb1 = _prep_mask(mask, torch.empty((b, h, tn, total), device='meta'))
-    if transposed:
-        ldw = (tn + 31) // 32
-        bits = torch.empty(b, total, ldw, dtype=torch.int32, device=device)
-        _native.check(lib.ddp_pack_mask_t(ctypes.c_void_p(mu8.data_ptr()), b, tn, total, m_ld, m_sb1,
-                                          ctypes.c_void_p(bits.data_ptr()), ldw, _g._stream()))
-        sb1w = total * ldw
-    else:
-        ldw = (total + 31) // 32
-        bits = torch.empty(b, tn, ldw, dtype=torch.int32, device=device)
-        _native.check(lib.ddp_pack_mask(ctypes.c_void_p(mu8.data_ptr()), b, tn, total, m_ld, m_sb1,
-                                        ctypes.c_void_p(bits.data_ptr()), ldw, _g._stream()))
-        sb1w = tn * ldw
+    t = 1 if transposed else 0
+    words = lib.ddp_attn_mask_words(b, tn, total, t)
+    bits = torch.empty(words, dtype=torch.int32, device=device)
+    _native.check(lib.ddp_attn_pack_mask(ctypes.c_void_p(mu8.data_ptr()), b, tn, total, m_ld, m_sb1,
+                                         ctypes.c_void_p(bits.data_ptr()), t, _g._stream()))
     _native.count_launch()
-    return bits, ldw, sb1w
+    ldw = ((tn if transposed else total) + 31) // 32
+    return bits, ldw, words // b
 
 
 def flash_attention_backward(k4, q4, v4, g4, neg_lse, nds, mask, scale, offset, dk4, dq4, dv4, bits=None):
@@ -185,7 +181,7 @@ def flash_attention_backward(k4, q4, v4, g4, neg_lse, nds, mask, scale, offset, 
         if bits is None:
             bits, ldw, sb1w = _pack_mask(mask, b, h, tn, total, k4.device)
         else:
-            ldw, sb1w = bits.size(-1), tn * bits.size(-1)
+            ldw, sb1w = (total + 31) // 32, bits.numel() // b
         bits_t, ldwt, sb1wt = _pack_mask(mask, b, h, tn, total, k4.device, transposed=True)
     va, vb, vv, vg = _g.as_view(k4), _g.as_view(q4), _g.as_view(v4), _g.as_view(g4)
     vda, vdb, vdv = _g.as_view(dk4), _g.as_view(dq4), _g.as_view(dv4)

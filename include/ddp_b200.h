@@ -114,7 +114,7 @@ int ddp_gemm_ex(int op, const ddp_tensor* A, const ddp_tensor* B, const ddp_tens
  * d and dv multiples of 8 and <= 64, scale > 0.  Scores stay in TMEM, probabilities go through shared memory
  * back into the tensor core (online softmax); the [M x T] slab is never written.  lse (optional, fp32
  * [b1][b0][M]) receives log2(sum_j exp(scale * s_ij)) = row max + log2(row sum) in the log2 domain.
- * mask_bits as for the softmax epilogues (ddp_pack_mask; bit set = masked out; NULL = no mask); a fully masked
+ * mask_bits: packed by ddp_attn_pack_mask(transposed = 0) (bit set = masked out; NULL = no mask); a fully masked
  * row is NaN as in the reference.  comm as for ddp_gemm (workspace / flag sizes: ddp_attn_fwd_workspace).
  * Errors -6: shape or dtype outside what this kernel covers (callers fall back to the three-kernel path). */
 int ddp_attn_fwd_workspace(const ddp_tensor* B, const ddp_tensor* V, int world, int chunk_rows, size_t* ws_bytes,
@@ -129,8 +129,7 @@ int ddp_attn_fwd(const ddp_tensor* A, const ddp_tensor* B, const ddp_tensor* V, 
  *          (all-gather of B, V AND the reduce-scatter of the per-rank partial sums fused in)
  * with P_ij = exp2(scale*log2e*A_i.B_j + neg_lse_i), dS_ij = P_ij*(scale*dO_i.V_j + nds_i); G = dO.
  * neg_lse = -L and nds = -scale*rowsum(dO*O) are fp32 [b1][b0][stat_ld] arrays, stat_ld a multiple of 64 >= M
- * (rows past M are read but ignored).  mask_bits: as for ddp_attn_fwd; mask_bits_t: the TRANSPOSED packing of
- * ddp_pack_mask_t ([b1][T][ld_words], bits along the rows).  Same shape limits as ddp_attn_fwd (error -6).
+ * (rows past M are read but ignored).  mask_bits: as for ddp_attn_fwd; mask_bits_t: ddp_attn_pack_mask(transposed = 1).  Same shape limits as ddp_attn_fwd (error -6).
  * ddp_attn_bwd_rows uses the workspace of ddp_attn_fwd_workspace; ddp_attn_bwd_cols its own. */
 int ddp_attn_bwd_rows(const ddp_tensor* A, const ddp_tensor* G, const ddp_tensor* B, const ddp_tensor* V,
                       const ddp_tensor* dA, const float* neg_lse, const float* nds, int64_t stat_ld,
@@ -142,10 +141,17 @@ int ddp_attn_bwd_cols(const ddp_tensor* A, const ddp_tensor* G, const ddp_tensor
                       const ddp_tensor* dV, const ddp_tensor* dB, const float* neg_lse, const float* nds,
                       int64_t stat_ld, const uint32_t* mask_bits_t, int64_t mask_ld_words, int64_t mask_sb1_words,
                       float scale, const ddp_comm* comm, int dbg, void* stream);
-/* bits_t[b1][cols][ld_words] <- mask u8 [b1][rows][cols]: bit (r & 31) of word r >> 5 = mask[r][col] != 0;
- * bits past `rows` are set. */
-int ddp_pack_mask_t(const uint8_t* mask, int64_t b1, int64_t rows, int64_t cols, int64_t mask_ld, int64_t mask_sb1,
-                    uint32_t* bits_t, int64_t ld_words, void* stream);
+/* Bit-packed masks of the attention kernels (bit set = masked out; elements outside the mask count as masked).
+ * The kernels' threads own one row (ddp_attn_fwd, ddp_attn_bwd_rows) or one column (ddp_attn_bwd_cols) each and
+ * read one 32-bit word per 32 elements of the other axis, so the words of 32 neighbouring rows (columns) are
+ * interleaved and a warp's loads coalesce:
+ *   transposed = 0: bits[b1][ceil(rows/32)][ld_words = ceil(cols/32)][32], bit k of word w of row r <- mask[r][32w+k]
+ *   transposed = 1: bits[b1][ceil(cols/32)][ld_words = ceil(rows/32)][32], bit k of word w of col c <- mask[32w+k][c]
+ * mask is uint8 [b1][rows][cols] (row stride mask_ld, batch stride mask_sb1).  ddp_attn_mask_words gives the
+ * size of `bits` in 32-bit words; the kernels take ld_words and the per-b1 stride (mask_words / b1). */
+size_t ddp_attn_mask_words(int64_t b1, int64_t rows, int64_t cols, int transposed);
+int ddp_attn_pack_mask(const uint8_t* mask, int64_t b1, int64_t rows, int64_t cols, int64_t mask_ld, int64_t mask_sb1,
+                       uint32_t* bits, int transposed, void* stream);
 int ddp_debug_timeout_site_attn(void); /* pipeline watchdog of the attention kernels (sites 11-40) */
 
 /* Row softmax over the last dim of x[b1][b0][rows][cols] with fused scale and boolean mask:
