@@ -225,6 +225,7 @@ def main():
                     sys.stderr.write('slab-free attention self-check failed: %s\n' % e)
                     att.FLASH_TRAIN = False
                 attention_path = 'slab-free (flash)' if att.FLASH_TRAIN else 'slab (self-check rejected slab-free path)'
+        torch.cuda.reset_peak_memory_stats()  # the self-check's slab step must not count as this path's peak
         for _ in range(max(args.warmup, 3)):
             step(x_dev, y_dev)
         barrier()

@@ -376,22 +376,29 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd_rows_kernel(const __gr
       if (p.mask_bits != nullptr)  // interleaved layout: the 32 rows of a warp read consecutive words
         mrow = p.mask_bits + b1i * p.mb_sb1 + static_cast<long long>(row_c >> 5) * p.mb_ld * 32 + (row_c & 31);
       // mask word of this row for the 32 columns of step jj, fetched one step ahead (see the forward kernel)
-      auto mask_word = [&](int jj) -> uint32_t {
-        if (mrow == nullptr || jj >= nj) return 0u;
-        const int si = jj / p.n_steps, nb = jj - si * p.n_steps;
-        const int seg = (p.rank + si) % p.world;
-        const int n0 = nb * kAbStep + h * 32;
-        if (p.Tn - n0 <= 0) return 0u;
-        return __ldg(mrow + ((static_cast<long long>(seg) * p.Tn + n0) >> 5) * 32);
+      int pf_nb = 0, pf_si = 0;  // cursor of the prefetch (no integer divisions in the step loop)
+      auto mask_word_next = [&]() -> uint32_t {
+        uint32_t o = 0u;
+        if (mrow == nullptr || pf_si >= p.world) return o;
+        int seg = p.rank + pf_si;
+        if (seg >= p.world) seg -= p.world;
+        const int n0 = pf_nb * kAbStep + h * 32;
+        if (p.Tn - n0 > 0) o = __ldg(mrow + ((static_cast<long long>(seg) * p.Tn + n0) >> 5) * 32);
+        if (++pf_nb == p.n_steps) {
+          pf_nb = 0;
+          ++pf_si;
+        }
+        return o;
       };
-      uint32_t mk_next = mask_word(0);
+      uint32_t mk_next = mask_word_next();
+      int cur_nb = 0;
       for (int j = 0; j < nj; ++j) {
         {
-          const int nb = j % p.n_steps;
-          const int n0 = nb * kAbStep + h * 32;
+          const int n0 = cur_nb * kAbStep + h * 32;
+          if (++cur_nb == p.n_steps) cur_nb = 0;
           const int nvalid = max(0, min(32, p.Tn - n0));
           uint32_t mk = mk_next;
-          mk_next = mask_word(j + 1);
+          mk_next = mask_word_next();
           if (nvalid < 32) mk |= (nvalid <= 0) ? 0xffffffffu : (0xffffffffu << nvalid);
           mbar_wait(&s_full[w], sf_ph, 27);
           sf_ph ^= 1;
@@ -778,13 +785,22 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd_cols_kernel(const __gr
             const float ndv[4] = {__uint_as_float(nd.x), __uint_as_float(nd.y), __uint_as_float(nd.z),
                                   __uint_as_float(nd.w)};
             float pv[4], dv4[4];
+            if (mk == 0u) {  // nothing masked in this thread's 32 rows: no per-element selects
 #pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              const int ee = c * 4 + e;
-              const bool dead = (mk >> ee) & 1u;
-              const float pe = dead ? 0.f : ex2_approx(fmaf(__uint_as_float(rs[ee]), p.scale_log2, nlv[e]));
-              pv[e] = pe;
-              dv4[e] = dead ? 0.f : pe * fmaf(__uint_as_float(rp[ee]), p.scale, ndv[e]);
+              for (int e = 0; e < 4; ++e) {
+                const int ee = c * 4 + e;
+                pv[e] = ex2_approx(fmaf(__uint_as_float(rs[ee]), p.scale_log2, nlv[e]));
+                dv4[e] = pv[e] * fmaf(__uint_as_float(rp[ee]), p.scale, ndv[e]);
+              }
+            } else {
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                const int ee = c * 4 + e;
+                const bool dead = (mk >> ee) & 1u;
+                const float pe = dead ? 0.f : ex2_approx(fmaf(__uint_as_float(rs[ee]), p.scale_log2, nlv[e]));
+                pv[e] = pe;
+                dv4[e] = dead ? 0.f : pe * fmaf(__uint_as_float(rp[ee]), p.scale, ndv[e]);
+              }
             }
             pp[c2 * 2] = pack2<T>(pv[0], pv[1]);
             pp[c2 * 2 + 1] = pack2<T>(pv[2], pv[3]);

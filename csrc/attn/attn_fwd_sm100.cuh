@@ -387,27 +387,33 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_fwd_kernel(const __grid_co
       float m_used = -INFINITY, l = 0.f;
       // mask words of this row for the 64 columns of step jj (bit set = masked out); fetched ONE STEP AHEAD so
       // that their L2 latency never sits between the arrival of S and the exponentials
-      auto mask_words = [&](int jj, uint32_t (&o)[2]) {
+      int pf_nb = 0, pf_si = 0;  // cursor of the prefetch (no integer divisions in the step loop)
+      auto mask_words_next = [&](uint32_t (&o)[2]) {
         o[0] = 0u;
         o[1] = 0u;
-        if (mrow == nullptr || jj >= nj) return;
-        const int si = jj / p.n_blocks, nb = jj - si * p.n_blocks;
-        const int seg = (p.rank + si) % p.world;
-        const int n0 = nb * kAtBN + h * 64;
+        if (mrow == nullptr || pf_si >= p.world) return;
+        int seg = p.rank + pf_si;
+        if (seg >= p.world) seg -= p.world;
+        const int n0 = pf_nb * kAtBN + h * 64;
         const int nvalid = p.Tn - n0;
         const uint32_t* mp = mrow + ((static_cast<long long>(seg) * p.Tn + n0) >> 5) * 32;
         if (nvalid > 0) o[0] = __ldg(mp);
         if (nvalid > 32) o[1] = __ldg(mp + 32);
+        if (++pf_nb == p.n_blocks) {
+          pf_nb = 0;
+          ++pf_si;
+        }
       };
       uint32_t mk_next[2];
-      mask_words(0, mk_next);
+      mask_words_next(mk_next);
+      int cur_nb = 0;
       for (int j = 0; j < nj; ++j) {
         {
-          const int nb = j % p.n_blocks;
-          const int n0 = nb * kAtBN + h * 64;                  // first column of this thread's half
+          const int n0 = cur_nb * kAtBN + h * 64;              // first column of this thread's half
+          if (++cur_nb == p.n_blocks) cur_nb = 0;
           const int nvalid = max(0, min(64, p.Tn - n0));
           uint32_t mk[2] = {mk_next[0], mk_next[1]};
-          mask_words(j + 1, mk_next);
+          mask_words_next(mk_next);
           if (nvalid < 64) {
 #pragma unroll
             for (int i = 0; i < 2; ++i) {

@@ -635,7 +635,7 @@ int main(int argc, char** argv) {
     run_case(c, argc > 14 ? atoi(argv[14]) : 0, true);
     return g_fail ? 1 : 0;
   }
-  if (mode != "perf" && mode != "bwd" && mode != "bwdfull") {
+  if (mode != "perf" && mode != "bwd" && mode != "bwdfull" && mode != "prof") {
     const int bf = DDP_BF16;
     //        dt  W b1 b0 M    Tn   d   dv  il     mask chunk ramp
     // stage 1: linear mode (no max / exp): isolates S MMA -> P staging -> PV MMA -> O store
@@ -666,6 +666,11 @@ int main(int argc, char** argv) {
       run_case({bf, 4, 1, 3, 100, 96, 64, 64, false, 1, 32, 0}, 0, true);
     }
     printf("SUMMARY pass=%d fail=%d\n", g_pass, g_fail);
+  }
+  if (mode == "prof") {  // exactly one launch of every attention kernel on the flagship per-GPU shape (for ncu)
+    perf_case(DDP_BF16, 16, 8192, 8192, 64, true, 1);
+    perf_bwd(DDP_BF16, 16, 8192, 8192, 64, 1, true);
+    return 0;
   }
   if (mode == "bwd" || mode == "bwdfull") {
     const int bf = DDP_BF16;

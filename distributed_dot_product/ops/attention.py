@@ -14,6 +14,8 @@ Memory: the probability slab ``P`` is kept for backward (as in the reference, wh
 of the ``dO V^T`` kernel (``delta = rowsum(dO * O)``, the flash-attention identity), so the backward makes
 five passes over a slab instead of nine.
 """
+import weakref
+
 import torch
 
 from distributed_dot_product import _native
@@ -143,6 +145,10 @@ def flash_attention_forward(k4, q4, v4, mask, scale, offset, out4, want_lse=Fals
     return lse
 
 
+#: packed masks of the most recent calls, keyed by mask object identity (see _pack_mask)
+_MASK_CACHE = {}
+
+
 def _pack_mask(mask, b, h, tn, total, device, transposed=False):
     """Bit-packs a bool ``[B, T/N, T]`` mask (True = masked out) for the attention kernels
     (``ddp_attn_pack_mask``): one word per 32 columns of a row for the row-side kernels, or - ``transposed`` - per
@@ -151,14 +157,28 @@ def _pack_mask(mask, b, h, tn, total, device, transposed=False):
     import ctypes
     from distributed_dot_product.ops.softmax import _prep_mask
     lib = _native.load()
-    mu8, m_ld, m_sb1 = _prep_mask(mask, torch.empty((b, h, tn, total), device='meta'))
     t = 1 if transposed else 0
+    ldw = ((tn if transposed else total) + 31) // 32
+    # A mask is usually the same tensor step after step (causal / padding masks): the packed words are cached per
+    # (storage, version counter, geometry) so that steady-state steps do not re-read the [T/N, T] byte mask.
+    # Identity of the tensor OBJECT (weak reference) + its version counter: a new mask that merely lands on the
+    # address of a freed one never matches.
+    key = (id(mask), t, b, tn, total)
+    hit = _MASK_CACHE.get(key)
+    if hit is not None:
+        ref, version, cached = hit
+        if ref() is mask and version == mask._version:
+            return cached, ldw, cached.numel() // b
+        del _MASK_CACHE[key]
+    mu8, m_ld, m_sb1 = _prep_mask(mask, torch.empty((b, h, tn, total), device='meta'))
     words = lib.ddp_attn_mask_words(b, tn, total, t)
     bits = torch.empty(words, dtype=torch.int32, device=device)
     _native.check(lib.ddp_attn_pack_mask(ctypes.c_void_p(mu8.data_ptr()), b, tn, total, m_ld, m_sb1,
                                          ctypes.c_void_p(bits.data_ptr()), t, _g._stream()))
     _native.count_launch()
-    ldw = ((tn if transposed else total) + 31) // 32
+    if len(_MASK_CACHE) >= 4:
+        _MASK_CACHE.pop(next(iter(_MASK_CACHE)))
+    _MASK_CACHE[key] = (weakref.ref(mask), mask._version, bits)
     return bits, ldw, words // b
 
 

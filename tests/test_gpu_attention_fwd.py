@@ -148,3 +148,28 @@ def test_attention_backward_harness_emulated_ranks(cuda_device):
     tail = '\n'.join(r.stdout.splitlines()[-20:])
     assert r.returncode == 0, tail
     assert 'fail=0' in r.stdout, tail
+
+
+def test_packed_mask_cache_follows_mask_contents(cuda_device):
+    """The packed-mask cache is keyed by tensor identity + version counter: an in-place update of the mask and a
+    brand-new mask tensor must both be seen by the next call."""
+    from distributed_dot_product.ops.attention import attention_core
+    torch.manual_seed(4)
+    b, heads, tn, d = 1, 2, 128, 32
+    k, q, v = (torch.randn(b, tn, heads * d, device=cuda_device).to(torch.bfloat16) for _ in range(3))
+    scale = 1.0 / math.sqrt(d)
+    mask = torch.zeros(b, tn, tn, dtype=torch.bool, device=cuda_device)
+    with torch.no_grad():
+        o1 = attention_core(k, q, v, mask, heads, scale, 64).float()
+        o1b = attention_core(k, q, v, mask, heads, scale, 64).float()     # cache hit
+        mask[:, :, tn // 2:] = True                                      # in place: version counter moves
+        o2 = attention_core(k, q, v, mask, heads, scale, 64).float()
+        del mask
+        mask3 = torch.zeros(b, tn, tn, dtype=torch.bool, device=cuda_device)   # may reuse the freed storage
+        o3 = attention_core(k, q, v, mask3, heads, scale, 64).float()
+    assert torch.equal(o1, o1b)
+    ref2 = _reference(k, q, v, torch.cat([torch.zeros(b, tn, tn // 2, dtype=torch.bool, device=cuda_device),
+                                          torch.ones(b, tn, tn // 2, dtype=torch.bool, device=cuda_device)], -1),
+                      heads, scale)
+    assert (o2 - ref2).abs().max().item() <= 2e-2 * max(1.0, ref2.abs().max().item())
+    assert torch.equal(o3, o1)
