@@ -85,8 +85,9 @@ def test_module_inference_uses_flash_and_matches_training_path(cuda_device):
     with torch.no_grad():
         infer_out = m(x, x, x, mask)
     launches = _native.launch_count - before
-    # 4 projections + mask packing + ONE attention kernel (the training path needs 3 kernels for the core)
-    assert launches == 6, launches
+    # 4 projections + ONE attention kernel (the slab path needs 3 kernels for the core); the mask was packed by
+    # the training call above and is served from the packed-mask cache (else one more launch)
+    assert launches in (5, 6), launches
     err = (infer_out.float() - train_out.float()).abs().max().item()
     assert err <= 3e-2 * max(1.0, train_out.float().abs().max().item()), err
 
