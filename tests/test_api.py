@@ -117,3 +117,43 @@ def test_debug_measure_prints(capsys, monkeypatch):
 def test_native_library_contract():
     from distributed_dot_product import _native
     assert _native.lib_path().endswith('libddp_b200.so')
+
+
+def test_example_script_runs_single_process():
+    """example.py (reference: example.py:1-33) end to end in one CPU process."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, CUDA_VISIBLE_DEVICES='', MASTER_ADDR='127.0.0.1')
+    for k in ('RANK', 'WORLD_SIZE', 'LOCAL_RANK'):
+        env.pop(k, None)
+    r = subprocess.run([sys.executable, os.path.join(root, 'example.py')], cwd=root, env=env, timeout=600,
+                       stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    assert r.returncode == 0, r.stdout[-2000:]
+    assert 'loss' in r.stdout and '(1, 4096, 768)' in r.stdout, r.stdout[-500:]
+
+
+def test_distributed_matmul_block_single_process():
+    """The reference's dead helper (functions.py:151-157) works here: local product (+ sum over ranks)."""
+    from distributed_dot_product.multiplication.functions import distributed_matmul_block
+    a, b = torch.rand(2, 5, 7), torch.rand(2, 7, 3)
+    assert torch.allclose(distributed_matmul_block(a, b), a @ b)
+    assert torch.allclose(distributed_matmul_block(a, b, transpose=True), (a @ b).transpose(-1, -2))
+
+
+def test_flash_eligibility_rules():
+    """Which operands the slab-free attention kernels accept (everything else takes the slab path)."""
+    from distributed_dot_product.ops.attention import _heads, flash_eligible
+    def ops(dtype, hd, heads, tn=64):
+        x = torch.zeros(1, tn, hd, dtype=dtype)
+        return _heads(x, heads), _heads(x, heads), _heads(x, heads)
+    assert flash_eligible(*ops(torch.bfloat16, 1024, 16), None, 1)
+    assert flash_eligible(*ops(torch.float16, 64, 2), None, 1)
+    assert not flash_eligible(*ops(torch.float32, 1024, 16), None, 1)          # tf32 tensors: slab path
+    assert not flash_eligible(*ops(torch.bfloat16, 1024, 4), None, 1)          # head dim 256 > 64
+    assert not flash_eligible(*ops(torch.bfloat16, 24, 2), None, 1)            # head dim 12: not a multiple of 8
+    mask = torch.zeros(1, 48, 96, dtype=torch.bool)
+    assert flash_eligible(*ops(torch.bfloat16, 128, 2, tn=64), mask, 1)
+    assert not flash_eligible(*ops(torch.bfloat16, 128, 2, tn=48), mask, 2)    # masked, world > 1: T/N % 32 != 0
+    assert not flash_eligible(*ops(torch.bfloat16, 128, 2), mask.float(), 1)   # only bool masks
