@@ -61,5 +61,47 @@ timed('nt + fused softmax bwd -> dS', lambda: G.gemm(_native.OP_NT, k4, q4, offs
                                                    softmax_bwd=(slab, delta, 0.125)), 2)
 timed('tn P^T.dO (reduce-scatter)', lambda: G.gemm(_native.OP_TN, slab, k4, out=out4), 1)
 timed('all dS.gather(Q)', lambda: G.gemm(_native.OP_NN, slab2, q4, offset=1024, out=out4), 1)
+
+# ---- slab-free attention kernels on the same operands (no slab traffic: report algorithmic TFLOP/s instead)
+import distributed_dot_product.ops.attention as A  # noqa: E402
+
+
+def timed_flops(name, fn, flops, iters=5):
+    for _ in range(2):
+        fn()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        fn()
+    e1.record()
+    e1.synchronize()
+    ms = torch.tensor([e0.elapsed_time(e1) / iters], device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    if rank == 0:
+        print(json.dumps({'kernel': name, 'n_gpus': world, 'T': T, 'ms': round(ms.item(), 4),
+                          'TFLOPs': round(flops / ms.item() * 1e-9, 1)}), flush=True)
+
+
+del slab, slab2
+v4 = q4
+g4 = k4
+pair = 2.0 * H * TN * T * D  # one 128x128xd product over the whole block of the score matrix
+stat_ld = (TN + 63) // 64 * 64
+neg_lse = torch.zeros(1, H, stat_ld, device=dev)
+nds = torch.zeros(1, H, stat_ld, device=dev)
+dk = torch.empty_like(k)
+dq = torch.empty_like(k)
+dv = torch.empty_like(k)
+h4 = lambda t: t.view(1, TN, H, D).transpose(1, 2)  # noqa: E731
+timed_flops('attn_fwd (slab-free)', lambda: A.flash_attention_forward(k4, q4, v4, mask, 0.125, 1024, out4), 2 * pair)
+lse = A.flash_attention_forward(k4, q4, v4, mask, 0.125, 1024, out4, want_lse=True)
+neg_lse[..., :TN] = -lse
+timed_flops('attn_bwd rows + cols (slab-free)',
+            lambda: A.flash_attention_backward(k4, q4, v4, g4, neg_lse, nds, mask, 0.125, 1024, h4(dk), h4(dq), h4(dv)),
+            7 * pair)
 comm.synchronize()
 comm.shutdown()
