@@ -1,7 +1,7 @@
 // Standalone validation + timing harness for ddp_attn_fwd (no Python).  Runs on ONE GPU; multi-rank cases are
 // emulated like in gemm_harness.cu: every "rank" owns its workspace / flags on the same GPU, the produce phase of
 // all ranks runs before the consume phase.
-// Usage: attn_harness [quick|full|perf|one dt W b1 b0 M Tn d dv il maskmode chunk ramp dbg]
+// Usage: attn_harness [quick|full|perf|bwd|bwdfull|multi|prof|one dt W b1 b0 M Tn d dv il maskmode chunk ramp dbg]
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>
@@ -635,7 +635,7 @@ int main(int argc, char** argv) {
     run_case(c, argc > 14 ? atoi(argv[14]) : 0, true);
     return g_fail ? 1 : 0;
   }
-  if (mode != "perf" && mode != "bwd" && mode != "bwdfull" && mode != "prof") {
+  if (mode != "perf" && mode != "bwd" && mode != "bwdfull" && mode != "prof" && mode != "multi") {
     const int bf = DDP_BF16;
     //        dt  W b1 b0 M    Tn   d   dv  il     mask chunk ramp
     // stage 1: linear mode (no max / exp): isolates S MMA -> P staging -> PV MMA -> O store
@@ -666,6 +666,16 @@ int main(int argc, char** argv) {
       run_case({bf, 4, 1, 3, 100, 96, 64, 64, false, 1, 32, 0}, 0, true);
     }
     printf("SUMMARY pass=%d fail=%d\n", g_pass, g_fail);
+  }
+  if (mode == "multi") {  // more work items than CTAs: every barrier phase / ring slot is carried across items
+    const int bf = DDP_BF16;
+    //        dt  W b1 b0  M     Tn   d   dv  il    mask chunk ramp
+    run_case({bf, 1, 1, 16, 2560, 128, 64, 64, true, 1, 64, 1}, 0, true);       // forward: 160 items
+    run_bwd_case({bf, 1, 1, 16, 2560, 128, 64, 64, true, 1, 64, 0}, true);      // row side: 160 items
+    run_bwd_case({bf, 1, 1, 16, 128, 2560, 64, 64, true, 1, 64, 0}, true);      // column side: 160 items
+    run_bwd_case({bf, 2, 1, 16, 128, 1280, 64, 64, true, 0, 256, 0}, true);     // column side, 2 ranks: 2 x 80 items
+    printf("SUMMARY-MULTI pass=%d fail=%d\n", g_pass, g_fail);
+    return g_fail ? 1 : 0;
   }
   if (mode == "prof") {  // exactly one launch of every attention kernel on the flagship per-GPU shape (for ncu)
     perf_case(DDP_BF16, 16, 8192, 8192, 64, true, 1);
