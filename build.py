@@ -34,6 +34,9 @@ HEADERS = [
     "csrc/attn/attn_bwd_sm100.cuh",
 ]
 LIB_OUT = "distributed_dot_product/_lib/libddp_b200.so"
+# `python build.py trace`: separate objects + build/attn_harness_trace with the pipeline time stamps of the
+# attention forward compiled in (ddp_attn_debug_trace); the production library never carries them.
+TRACE = False
 
 
 def _newer(src_list, out):
@@ -55,10 +58,10 @@ def _run(cmd, log=None):
 
 
 def compile_obj(src):
-    obj = os.path.join(ROOT, "build/obj", src.replace("/", "_") + ".o")
+    obj = os.path.join(ROOT, "build/obj_trace" if TRACE else "build/obj", src.replace("/", "_") + ".o")
     os.makedirs(os.path.dirname(obj), exist_ok=True)
     if _newer([src] + HEADERS, obj):
-        _run([NVCC] + FLAGS + ["-c", src, "-o", obj], log=obj + ".log")
+        _run([NVCC] + FLAGS + (["-DDDP_ATTN_TRACE"] if TRACE else []) + ["-c", src, "-o", obj], log=obj + ".log")
     return obj
 
 
@@ -83,7 +86,7 @@ def build_harness():
         src = "csrc/tests/%s.cu" % name
         if not os.path.exists(os.path.join(ROOT, src)):
             continue
-        out = os.path.join(ROOT, "build", name)
+        out = os.path.join(ROOT, "build", name + ("_trace" if TRACE else ""))
         if _newer([src] + HEADERS + [os.path.relpath(o, ROOT) for o in objs], out):
             _run([NVCC] + ARCH + ["-O2", "-std=c++17", src, "-o", out] + objs)
         print("built build/" + name)
@@ -119,6 +122,10 @@ def dump_sass():
 
 
 if __name__ == "__main__":
+    if "trace" in sys.argv[1:]:
+        TRACE = True
+        build_harness()
+        sys.exit(0)
     build_lib()
     if "harness" in sys.argv[1:]:
         build_harness()

@@ -1,5 +1,6 @@
 // Host side of the slab-free attention forward: shape checks, TMA tensor maps, launch.
 // C ABI declared in include/ddp_b200.h.
+#include <cstdlib>
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
 
@@ -12,7 +13,7 @@
 namespace ddp {
 
 constexpr int kAtStages = 3;
-constexpr int kAtSmem = 2 * kAtTile + 2 * kAtPBytes + kAtStages * kAtStageBytes + (2 * kAtStages + 14) * 8 + 16 + 4 * 128 * 8 + 1024;
+constexpr int kAtSmem = 2 * kAtTile + 2 * kAtPBytes + kAtStages * kAtStageBytes + (2 * kAtStages + 22) * 8 + 16 + 4 * 128 * 8 + 1024;
 static_assert(kAtSmem <= 232448, "shared memory budget exceeded");
 
 static int attn_check(const ddp_tensor* A, const ddp_tensor* B, const ddp_tensor* V, int world) {
@@ -40,6 +41,18 @@ static int tile_map(CUtensorMap* m, const ddp_tensor* t, uint32_t box_rows, bool
   if (t->b1 == 1) strides[3] = strides[2];
   return make_map(m, t->dtype, t->ptr, dims, strides, box, mn_major);
 }
+
+// DDP_ATTN_DBG=<bits> ORs experiment bits into the dbg argument of the three attention entry points (read once).
+static int attn_env_dbg() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("DDP_ATTN_DBG");
+    v = e ? atoi(e) : 0;
+  }
+  return v;
+}
+
+static long long* g_attn_trace = nullptr;  // ddp_attn_debug_trace
 
 template <int DT>
 static int attn_launch(const AttnKParams& p, int grid, cudaStream_t stream) {
@@ -80,6 +93,12 @@ extern "C" int ddp_attn_fwd_workspace(const ddp_tensor* B, const ddp_tensor* V, 
   return 0;
 }
 
+extern "C" void ddp_attn_debug_trace(long long* device_buf) { g_attn_trace = device_buf; }
+extern "C" int ddp_attn_debug_trace_dims(int* actors, int* steps, int* events) {
+  *actors = 8; *steps = kAtTraceSteps; *events = kAtTraceEvents;
+  return 0;
+}
+
 extern "C" int ddp_debug_timeout_site_attn(void) {
   unsigned int v = 0, zero = 0;
   if (cudaMemcpyFromSymbol(&v, ddp::g_ddp_timeout_site, sizeof v) != cudaSuccess) return -1;
@@ -115,7 +134,8 @@ extern "C" int ddp_attn_fwd(const ddp_tensor* A, const ddp_tensor* B, const ddp_
   p.lse = lse;
   p.mask_bits = mask_bits; p.mb_ld = mask_ld_words; p.mb_sb1 = mask_sb1_words;
   p.scale_log2 = scale * 1.4426950408889634f;
-  p.dbg = dbg;
+  p.dbg = dbg | attn_env_dbg();
+  p.trace = g_attn_trace;
   const uint64_t Bt = (uint64_t)A->b0 * A->b1;
 
   if (int e = tile_map(&p.tmA, A, kAtBM, false)) return e;
@@ -265,7 +285,7 @@ extern "C" int ddp_attn_bwd_rows(const ddp_tensor* A, const ddp_tensor* G, const
   p.neg_lse = neg_lse; p.nds = nds; p.stat_ld = stat_ld;
   p.mask_bits = mask_bits; p.mb_ld = mask_ld_words; p.mb_sb1 = mask_sb1_words;
   p.scale = scale; p.scale_log2 = scale * 1.4426950408889634f;
-  p.dbg = dbg;
+  p.dbg = dbg | attn_env_dbg();
   if (int e = tile_map(&p.tmA, A, kAtBM, false)) return e;
   if (int e = tile_map(&p.tmG, G, kAtBM, false)) return e;
   if (int e = tile_map(&p.tmB, B, kAbStep, false)) return e;
@@ -445,7 +465,7 @@ extern "C" int ddp_attn_bwd_cols(const ddp_tensor* A, const ddp_tensor* G, const
   p.neg_lse = neg_lse; p.nds = nds; p.stat_ld = stat_ld;
   p.mask_bits = mask_bits_t; p.mb_ld = mask_ld_words; p.mb_sb1 = mask_sb1_words;
   p.scale = scale; p.scale_log2 = scale * 1.4426950408889634f;
-  p.dbg = dbg;
+  p.dbg = dbg | attn_env_dbg();
   if (int e = tile_map(&p.tmA, A, kAbStep, false)) return e;
   if (int e = tile_map(&p.tmG, G, kAbStep, false)) return e;
   if (int e = tile_map(&p.tmB, B, kAtBM, false)) return e;

@@ -181,7 +181,7 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd_rows_kernel(const __gr
   uint64_t* o_done = p_full + 2;     // [2] dA_w += dS_w B_j finished
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_done + 2);
 
-  const int warp = threadIdx.x >> 5;
+  const int warp = (p.dbg & 8) ? ((threadIdx.x >> 5) + 4) % (kAtThreads / 32) : (threadIdx.x >> 5);  // see the forward kernel
   const int lane = threadIdx.x & 31;
   const int Bt = p.b0 * p.b1;
   const bool dist = p.world > 1;
@@ -297,6 +297,47 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd_rows_kernel(const __gr
           dD[kk] = umma_smem_desc(smem_u32(sDS) + w * kAtTile + kk * 32, 16, 1024);
         }
         uint32_t g0 = 0;
+        const bool poll_test = (p.dbg & 2) != 0;  // see the forward kernel: dbg bit 2 / bit 4
+        auto poll = [&](uint64_t* bar, uint32_t parity) {
+          return poll_test ? mbar_test_wait(bar, parity) : mbar_try_wait(bar, parity);
+        };
+        if (p.dbg & 4) {
+          for (int it = blockIdx.x; it < items; it += gridDim.x) {
+            mbar_wait(a_full, a_ph, 24);
+            a_ph ^= 1;
+            tc_fence_after();
+            auto issue_s = [&](int j) {
+              const uint32_t g = g0 + j;
+              mbar_wait(&kv_full[g % STAGES], (g / STAGES) & 1, 44);
+              mbar_wait(&s_empty[w], se_ph ^ 1, 45);
+              se_ph ^= 1;
+              tc_fence_after();
+              const uint64_t db = umma_smem_desc(sKV_u + (g % STAGES) * kStage, 16, 1024);
+              const uint64_t dv = umma_smem_desc(sKV_u + (g % STAGES) * kStage + kAbHalfTile, 16, 1024);
+#pragma unroll
+              for (int kk = 0; kk < 4; ++kk) umma_ss<false>(tS_w, dA[kk], db + 2 * kk, kIdS, kk != 0 ? 1u : 0u);
+#pragma unroll
+              for (int kk = 0; kk < 4; ++kk) umma_ss<false>(tP_w, dG[kk], dv + 2 * kk, kIdS, kk != 0 ? 1u : 0u);
+              umma_commit(&s_full[w]);
+            };
+            issue_s(0);
+            for (int j = 0; j < nj; ++j) {
+              if (j + 1 < nj) issue_s(j + 1);
+              const uint32_t g = g0 + j;
+              mbar_wait(&p_full[w], pf_ph, 46);
+              pf_ph ^= 1;
+              tc_fence_after();
+              const uint64_t db = umma_smem_desc(sKV_u + (g % STAGES) * kStage, kAbHalfTile, 1024, 2);
+#pragma unroll
+              for (int kk = 0; kk < 4; ++kk)
+                umma_ss<false>(tA_w, dD[kk], db + 128 * kk, kIdA, (j | kk) != 0 ? 1u : 0u);
+              umma_commit(&o_done[w]);
+              umma_commit(&kv_empty[g % STAGES]);
+            }
+            umma_commit(a_empty);
+            g0 += static_cast<uint32_t>(nj);
+          }
+        } else
         for (int it = blockIdx.x; it < items; it += gridDim.x) {
           mbar_wait(a_full, a_ph, 24);
           a_ph ^= 1;
@@ -308,8 +349,8 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd_rows_kernel(const __gr
             bool progress = false;
             if (nS < nj) {
               const uint32_t g = g0 + nS;
-              if (nS >= kvr && mbar_try_wait(&kv_full[g % STAGES], (g / STAGES) & 1)) kvr = nS + 1;
-              if (nS < kvr && mbar_try_wait(&s_empty[w], se_ph ^ 1)) {
+              if (nS >= kvr && poll(&kv_full[g % STAGES], (g / STAGES) & 1)) kvr = nS + 1;
+              if (nS < kvr && poll(&s_empty[w], se_ph ^ 1)) {
                 se_ph ^= 1;
                 tc_fence_after();
                 const uint64_t db = umma_smem_desc(sKV_u + (g % STAGES) * kStage, 16, 1024);
@@ -323,7 +364,7 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd_rows_kernel(const __gr
                 progress = true;
               }
             }
-            if (nPV < nS && mbar_try_wait(&p_full[w], pf_ph)) {
+            if (nPV < nS && poll(&p_full[w], pf_ph)) {
               pf_ph ^= 1;
               tc_fence_after();
               const uint32_t g = g0 + nPV;
@@ -534,7 +575,7 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd_cols_kernel(const __gr
   uint64_t* o_done = p_full + 2;     // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_done + 2);
 
-  const int warp = threadIdx.x >> 5;
+  const int warp = (p.dbg & 8) ? ((threadIdx.x >> 5) + 4) % (kAtThreads / 32) : (threadIdx.x >> 5);  // see the forward kernel
   const int lane = threadIdx.x & 31;
   const int Bt = p.b0 * p.b1;
   const bool dist = p.world > 1;
@@ -658,6 +699,51 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd_cols_kernel(const __gr
           dDt[kk] = umma_smem_desc(smem_u32(sDt) + w * kAtTile + kk * 32, 16, 1024);
         }
         uint32_t g0 = 0;
+        const bool poll_test = (p.dbg & 2) != 0;  // see the forward kernel: dbg bit 2 / bit 4
+        auto poll = [&](uint64_t* bar, uint32_t parity) {
+          return poll_test ? mbar_test_wait(bar, parity) : mbar_try_wait(bar, parity);
+        };
+        if (p.dbg & 4) {
+          for (int it = blockIdx.x; it < items; it += gridDim.x) {
+            mbar_wait(a_full, a_ph, 34);
+            a_ph ^= 1;
+            tc_fence_after();
+            auto issue_s = [&](int j) {
+              const uint32_t g = g0 + j;
+              mbar_wait(&kv_full[g % STAGES], (g / STAGES) & 1, 47);
+              mbar_wait(&s_empty[w], se_ph ^ 1, 48);
+              se_ph ^= 1;
+              tc_fence_after();
+              const uint64_t da = umma_smem_desc(sKV_u + (g % STAGES) * kAbColsStage, 16, 1024);
+              const uint64_t dg = umma_smem_desc(sKV_u + (g % STAGES) * kAbColsStage + kAbHalfTile, 16, 1024);
+#pragma unroll
+              for (int kk = 0; kk < 4; ++kk) umma_ss<false>(tS_w, dB_[kk], da + 2 * kk, kIdS, kk != 0 ? 1u : 0u);
+#pragma unroll
+              for (int kk = 0; kk < 4; ++kk) umma_ss<false>(tP_w, dV_[kk], dg + 2 * kk, kIdS, kk != 0 ? 1u : 0u);
+              umma_commit(&s_full[w]);
+            };
+            issue_s(0);
+            for (int j = 0; j < nj; ++j) {
+              if (j + 1 < nj) issue_s(j + 1);
+              const uint32_t g = g0 + j;
+              mbar_wait(&p_full[w], pf_ph, 49);
+              pf_ph ^= 1;
+              tc_fence_after();
+              const uint64_t da = umma_smem_desc(sKV_u + (g % STAGES) * kAbColsStage, kAbHalfTile, 1024, 2);
+              const uint64_t dg = umma_smem_desc(sKV_u + (g % STAGES) * kAbColsStage + kAbHalfTile, kAbHalfTile, 1024, 2);
+#pragma unroll
+              for (int kk = 0; kk < 4; ++kk)  // dV_w += P^T_w dO_i
+                umma_ss<false>(tV_w, dPt[kk], dg + 128 * kk, kIdO, (j | kk) != 0 ? 1u : 0u);
+#pragma unroll
+              for (int kk = 0; kk < 4; ++kk)  // dB_w += dS^T_w A_i
+                umma_ss<false>(tB_w, dDt[kk], da + 128 * kk, kIdO, (j | kk) != 0 ? 1u : 0u);
+              umma_commit(&o_done[w]);
+              umma_commit(&kv_empty[g % STAGES]);
+            }
+            umma_commit(a_empty);
+            g0 += static_cast<uint32_t>(nj);
+          }
+        } else
         for (int it = blockIdx.x; it < items; it += gridDim.x) {
           mbar_wait(a_full, a_ph, 34);
           a_ph ^= 1;
@@ -669,8 +755,8 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd_cols_kernel(const __gr
             bool progress = false;
             if (nS < nj) {
               const uint32_t g = g0 + nS;
-              if (nS >= kvr && mbar_try_wait(&kv_full[g % STAGES], (g / STAGES) & 1)) kvr = nS + 1;
-              if (nS < kvr && mbar_try_wait(&s_empty[w], se_ph ^ 1)) {
+              if (nS >= kvr && poll(&kv_full[g % STAGES], (g / STAGES) & 1)) kvr = nS + 1;
+              if (nS < kvr && poll(&s_empty[w], se_ph ^ 1)) {
                 se_ph ^= 1;
                 tc_fence_after();
                 const uint64_t da = umma_smem_desc(sKV_u + (g % STAGES) * kAbColsStage, 16, 1024);
@@ -684,7 +770,7 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd_cols_kernel(const __gr
                 progress = true;
               }
             }
-            if (nPV < nS && mbar_try_wait(&p_full[w], pf_ph)) {
+            if (nPV < nS && poll(&p_full[w], pf_ph)) {
               pf_ph ^= 1;
               tc_fence_after();
               const uint32_t g = g0 + nPV;

@@ -68,7 +68,22 @@ struct alignas(64) AttnKParams {
   long long push_ld[2], push_sb0[2], push_sb1[2];
   int push_rows, push_row_bytes[2];
   int dbg;  // bit 0 (harness): P = scale_log2 * S without max / exp / normalisation (linear, isolates the MMAs)
+  // Pipeline trace (ddp_attn_debug_trace; null in production): CTA 0 records clock64() of the events of the first
+  // kAtTraceSteps steps of its first work item, [actor][step][event]; actors 0-2 = softmax warps (w0 h0 q0),
+  // (w0 h1 q0), (w1 h0 q0), actors 3-4 = the MMA issuers of row blocks 0 / 1, actors 5-7 = softmax warps
+  // (w0 h0, q = 1, 2, 3).
+  long long* trace;
 };
+constexpr int kAtTraceSteps = 64;
+constexpr int kAtTraceEvents = 8;
+// Compiled in only with -DDDP_ATTN_TRACE (python build.py trace): the extra live values cost the softmax loop
+// registers it does not have (measured: 0.585 -> 0.76 ms for the forward kernel with the stamps compiled in).
+__device__ __forceinline__ void attn_trace(long long* buf, bool on, int actor, int step, int ev) {
+#ifdef DDP_ATTN_TRACE
+  if (buf != nullptr && on && step < kAtTraceSteps)
+    buf[(actor * kAtTraceSteps + step) * kAtTraceEvents + ev] = clock64();
+#endif
+}
 
 template <int DT, int STAGES, bool kRaw = false>
 __global__ void __launch_bounds__(kAtThreads, 1) attn_fwd_kernel(const __grid_constant__ AttnKParams p) {
@@ -89,10 +104,13 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_fwd_kernel(const __grid_co
   uint64_t* s_empty = s_full + 2;           // [2]  warpgroup w has read S_w
   uint64_t* p_full = s_empty + 2;           // [4]  half h of P_w staged (and O_{w,h} rescaled); index w*2+h
   uint64_t* o_done = p_full + 4;            // [4]  O_{w,h} += P_{w,h} V_j finished
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_done + 4);
+  uint64_t* pp = o_done + 4;                // [4][2] exp-phase token of lane quadrant q: [q][w] = row block w may run
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(pp + 8);
   float2* sStat = reinterpret_cast<float2*>(tmem_slot + 4);  // [2][2][128] (max, sum) of every stream, for the merge
 
-  const int warp = threadIdx.x >> 5;
+  // dbg bit 8: the four control warps (producer, issuers, pusher) are the LAST warpgroup of the CTA instead of the
+  // first (role index = (physical warp + 4) % 20; the softmax warps keep physical warp % 4 = TMEM lane quadrant)
+  const int warp = (p.dbg & 8) ? ((threadIdx.x >> 5) + 4) % (kAtThreads / 32) : (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
   const int Bt = p.b0 * p.b1;
   const bool dist = p.world > 1;
@@ -126,6 +144,7 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_fwd_kernel(const __grid_co
       mbar_init(&p_full[st], 4);
       mbar_init(&o_done[st], 1);
     }
+    for (int i = 0; i < 8; ++i) mbar_init(&pp[i], 2);  // the two warps (column halves) of the other row block
     fence_mbar_init();
   }
   if (warp == 2) tmem_alloc(tmem_slot, kAtTmemCols);
@@ -227,6 +246,51 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_fwd_kernel(const __grid_co
         dP[1][kk] = umma_smem_desc(smem_u32(sP) + w * kAtPBytes + kAtTile + kk * 32, 16, 1024);
       }
       uint32_t g0 = 0;  // steps issued by earlier work items: step j of this item uses ring slot (g0 + j) % STAGES
+      // dbg bit 2: the polls below use mbarrier.test_wait (never suspends) instead of try_wait;
+      // dbg bit 4: static schedule with blocking waits, in the order the events arrive in steady state
+      //            (S(j+1) as soon as the softmax warps hold S(j), then the two P.V products of step j)
+      const bool poll_test = (p.dbg & 2) != 0;
+      auto poll = [&](uint64_t* bar, uint32_t parity) {
+        return poll_test ? mbar_test_wait(bar, parity) : mbar_try_wait(bar, parity);
+      };
+      if (p.dbg & 4) {
+        for (int it = blockIdx.x; it < items; it += gridDim.x) {
+          mbar_wait(a_full, a_ph, 14);
+          a_ph ^= 1;
+          tc_fence_after();
+          auto issue_s = [&](int j) {
+            const uint32_t g = g0 + j;
+            mbar_wait(&kv_full[g % STAGES], (g / STAGES) & 1, 41);
+            mbar_wait(&s_empty[w], se_ph ^ 1, 42);
+            se_ph ^= 1;
+            tc_fence_after();
+            const uint64_t db = umma_smem_desc(sKV_u + (g % STAGES) * kAtStageBytes, 16, 1024);
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk) umma_ss<false>(tS_w, dA[kk], db + 2 * kk, kIdS, kk != 0 ? 1u : 0u);
+            umma_commit(&s_full[w]);
+          };
+          issue_s(0);
+          for (int j = 0; j < nj; ++j) {
+            if (j + 1 < nj) issue_s(j + 1);
+            const uint32_t g = g0 + j;
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+              mbar_wait(&p_full[w * 2 + h], pf_ph[h], 43);
+              pf_ph[h] ^= 1;
+              tc_fence_after();
+              const uint64_t dv = umma_smem_desc(
+                  sKV_u + (g % STAGES) * kAtStageBytes + kAtTile + h * (4 * 2048), kAtTile, 1024, 2);
+#pragma unroll
+              for (int kk = 0; kk < 4; ++kk)
+                umma_ss<false>(tO_w + h * 64, dP[h][kk], dv + 128 * kk, kIdO, (j | kk) != 0 ? 1u : 0u);
+              umma_commit(&o_done[w * 2 + h]);
+            }
+            umma_commit(&kv_empty[g % STAGES]);
+          }
+          umma_commit(a_empty);
+          g0 += static_cast<uint32_t>(nj);
+        }
+      } else
       for (int it = blockIdx.x; it < items; it += gridDim.x) {
         mbar_wait(a_full, a_ph, 14);
         a_ph ^= 1;
@@ -240,21 +304,22 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_fwd_kernel(const __grid_co
           bool progress = false;
           if (nS < nj) {
             const uint32_t g = g0 + nS;
-            if (nS >= kvr && mbar_try_wait(&kv_full[g % STAGES], (g / STAGES) & 1)) kvr = nS + 1;
-            if (nS < kvr && mbar_try_wait(&s_empty[w], se_ph ^ 1)) {
+            if (nS >= kvr && poll(&kv_full[g % STAGES], (g / STAGES) & 1)) kvr = nS + 1;
+            if (nS < kvr && poll(&s_empty[w], se_ph ^ 1)) {
               se_ph ^= 1;
               tc_fence_after();
               const uint64_t db = umma_smem_desc(sKV_u + (g % STAGES) * kAtStageBytes, 16, 1024);
 #pragma unroll
               for (int kk = 0; kk < 4; ++kk) umma_ss<false>(tS_w, dA[kk], db + 2 * kk, kIdS, kk != 0 ? 1u : 0u);
               umma_commit(&s_full[w]);
+              attn_trace(p.trace, blockIdx.x == 0 && it == 0, 3 + w, nS, 0);
               ++nS;
               progress = true;
             }
           }
 #pragma unroll
           for (int h = 0; h < 2; ++h) {
-            if (nPV[h] < nS && mbar_try_wait(&p_full[w * 2 + h], pf_ph[h])) {
+            if (nPV[h] < nS && poll(&p_full[w * 2 + h], pf_ph[h])) {
               pf_ph[h] ^= 1;
               tc_fence_after();
               const int j = nPV[h];
@@ -265,6 +330,7 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_fwd_kernel(const __grid_co
               for (int kk = 0; kk < 4; ++kk)
                 umma_ss<false>(tO_w + h * 64, dP[h][kk], dv + 128 * kk, kIdO, (j | kk) != 0 ? 1u : 0u);
               umma_commit(&o_done[w * 2 + h]);
+              attn_trace(p.trace, blockIdx.x == 0 && it == 0, 3 + w, j, 1 + h);
               nPV[h] = j + 1;
               progress = true;
             }
@@ -374,6 +440,14 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_fwd_kernel(const __grid_co
     const uint32_t sw = lane & 7;
     const uint32_t pair_bar = 1 + w * 4 + q;  // named barrier shared with the warp of the other column half
     uint32_t sf_ph = 0, od_ph = 0;
+    // Ping-pong of the exponential phase (dbg bit 32): the four softmax warps of a scheduler (lane quadrant q) are
+    // the two column halves of row block 0 and of row block 1.  Left alone they run in lock step - all four in
+    // the MUFU-bound exponential phase at once, then all four in the TMEM-load / max / wait phases with the MUFU
+    // idle.  The token makes the two row blocks alternate: block w runs its exponentials of step n only after
+    // block w^1 has finished those of step n-1 (w = 1) / n (w = 0), so the other block's loads, maxima and waits
+    // hide behind them.
+    const bool pingpong = (p.dbg & 32) != 0;
+    uint32_t pp_n = 0;
     for (int it = blockIdx.x; it < items; it += gridDim.x) {
       int b1i, b0i, m0;
       decode(it, b1i, b0i, m0);
@@ -425,9 +499,14 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_fwd_kernel(const __grid_co
               }
             }
           }
+          const bool tr_on = p.trace != nullptr && blockIdx.x == 0 && it == 0 && lane == 0 &&
+                             ((q == 0 && (w == 0 || h == 0)) || (w == 0 && h == 0));
+          const int tr_actor = q == 0 ? w * 2 + h : 4 + q;  // 0, 1, 2 and 5, 6, 7 = (w0 h0, q = 1, 2, 3)
+          attn_trace(p.trace, tr_on, tr_actor, j, 0);
           mbar_wait(&s_full[w], sf_ph, 17);
           sf_ph ^= 1;
           tc_fence_after();
+          attn_trace(p.trace, tr_on, tr_actor, j, 1);
           // ---- this thread's half row: one TMEM load, then S_w goes straight back to the MMA warp
           uint32_t r[64];
           tmem_ld_32x64(tS, r);
@@ -436,6 +515,7 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_fwd_kernel(const __grid_co
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(&s_empty[w]);
+          attn_trace(p.trace, tr_on, tr_actor, j, 2);
           // ---- maximum of the raw scores over the live columns (four independent chains)
           float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
 #pragma unroll
@@ -458,11 +538,13 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_fwd_kernel(const __grid_co
           // Lazy rescale: the reference point of the exponentials only moves when the maximum grew by more than
           // 2^kAtTau, so P stays <= 2^kAtTau and the O accumulator is rarely touched.
           const bool need = !kRaw && (m_blk > m_used + kAtTau);
+          attn_trace(p.trace, tr_on, tr_actor, j, 3);
           if (j > 0) {
             // O_st += P V_{j-1} has finished: our P rows may be overwritten, O_st may be rescaled
             mbar_wait(&o_done[st], od_ph, 18);
             od_ph ^= 1;
             tc_fence_after();
+            attn_trace(p.trace, tr_on, tr_actor, j, 4);
             if (__any_sync(0xffffffffu, need)) {
               const float f = need ? ex2_approx(m_used - m_blk) : 1.f;
 #pragma unroll
@@ -481,6 +563,7 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_fwd_kernel(const __grid_co
           }
           if (need) m_used = m_blk;
           const float neg_m = (kRaw || m_used == -INFINITY) ? 0.f : -m_used;
+          if (pingpong) mbar_wait(&pp[q * 2 + w], w == 0 ? ((pp_n & 1u) ^ 1u) : (pp_n & 1u), 50);
           // ---- P = exp2(scale_log2 * S - m) -> bf16 row in shared memory (K-major, 128B swizzle)
           float l0 = 0.f, l1 = 0.f, l2 = 0.f, l3 = 0.f;
 #pragma unroll
@@ -518,10 +601,17 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_fwd_kernel(const __grid_co
             }
           }
           l += (l0 + l1) + (l2 + l3);
+          if (pingpong) {
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&pp[q * 2 + (w ^ 1)]);
+            ++pp_n;
+          }
+          attn_trace(p.trace, tr_on, tr_actor, j, 5);
           tc_fence_before();           // a rescale of O_st (TMEM stores) precedes the MMA released below
           fence_proxy_async_smem();    // P (generic-proxy stores) -> tensor core (async proxy)
           __syncwarp();
           if (lane == 0) mbar_arrive(&p_full[st]);
+          attn_trace(p.trace, tr_on, tr_actor, j, 6);
         }
       }
       // ---- row block finished: merge the two column-half streams of every row, O = (Oa fa + Ob fb) / l

@@ -57,6 +57,22 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
+// Non-blocking probe of an mbarrier phase.  mbarrier.try_wait may SUSPEND the thread for a system-dependent time
+// when the phase is not complete; a thread that polls several barriers in turn (the MMA issuers of the attention
+// kernels) must use test_wait, or it sleeps on one barrier while another one completes.
+__device__ __forceinline__ bool mbar_test_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+      "selp.u32 %0, 1, 0, p;\n"
+      "}\n"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
 // Last pipeline wait that gave up (0 = none): see mbar_wait.  Read and cleared by ddp_debug_timeout_site().
 static __device__ unsigned int g_ddp_timeout_site = 0;
 

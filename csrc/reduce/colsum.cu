@@ -138,6 +138,8 @@ static __device__ __align__(256) float g_colsum_noalloc_scratch[DDP_COLSUM_NOALL
 // must never be passed to a kernel; the device address comes from cudaGetSymbolAddress, asked once per
 // device while that device is current.
 static int colsum_noalloc_scratch(float** out) {
+  // Written without a lock: two host threads that race on the first call for a device both ask the runtime and
+  // both store the same address (the symbol has one address per device), so the race is benign.
   static float* cached[64] = {};
   int dev = -1;
   if (int e = cuda_check(cudaGetDevice(&dev), "cudaGetDevice")) return e;

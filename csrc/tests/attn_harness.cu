@@ -1,7 +1,7 @@
 // Standalone validation + timing harness for ddp_attn_fwd (no Python).  Runs on ONE GPU; multi-rank cases are
 // emulated like in gemm_harness.cu: every "rank" owns its workspace / flags on the same GPU, the produce phase of
 // all ranks runs before the consume phase.
-// Usage: attn_harness [quick|full|perf|bwd|bwdfull|multi|prof|one dt W b1 b0 M Tn d dv il maskmode chunk ramp dbg]
+// Usage: attn_harness [quick|full|perf|perfall|bwd|bwdfull|multi|prof|one dt W b1 b0 M Tn d dv il maskmode chunk ramp dbg]
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>
@@ -296,7 +296,7 @@ static bool run_case(const Case& c, int dbg, bool verbose) {
 // ---------------------------------------------------------------------------------------------- backward
 // Validates ddp_attn_bwd_rows / ddp_attn_bwd_cols against a double-precision reference.  The row statistics
 // (-L, -scale*delta) come from the CPU reference, so the two kernels are tested independently of the forward.
-static bool run_bwd_case(const Case& c, bool verbose) {
+static bool run_bwd_case(const Case& c, bool verbose, int dbg = 0) {
   const int W = c.world, T = W * c.Tn;
   const float scale = 1.0f / sqrtf((float)c.d);
   const double sl2 = (double)scale * 1.4426950408889634;
@@ -634,6 +634,86 @@ int main(int argc, char** argv) {
     c.maskmode = atoi(argv[11]); c.chunk = atoi(argv[12]); c.ramp = atoi(argv[13]);
     run_case(c, argc > 14 ? atoi(argv[14]) : 0, true);
     return g_fail ? 1 : 0;
+  }
+  if (mode == "trace") {  // pipeline time stamps of CTA 0 (ddp_attn_debug_trace), flagship shape; dbg = argv[2]
+    int na, ns, ne;
+    ddp_attn_debug_trace_dims(&na, &ns, &ne);
+    const size_t n = (size_t)na * ns * ne;
+    long long* dbuf;
+    CK(cudaMalloc((void**)&dbuf, n * 8));
+    CK(cudaMemset(dbuf, 0, n * 8));
+    const int dbg = argc > 2 ? atoi(argv[2]) : 0;
+    const bool with_mask = argc > 3 ? atoi(argv[3]) != 0 : false;
+    perf_case(DDP_BF16, 16, 8192, 8192, 64, with_mask, 2, dbg);  // warm
+    ddp_attn_debug_trace(dbuf);
+    perf_case(DDP_BF16, 16, 8192, 8192, 64, with_mask, 1, dbg);
+    ddp_attn_debug_trace(nullptr);
+    std::vector<long long> h(n);
+    CK(cudaMemcpy(h.data(), dbuf, n * 8, cudaMemcpyDeviceToHost));
+    auto at = [&](int a, int s_, int e) { return h[((size_t)a * ns + s_) * ne + e]; };
+    const long long t0 = at(3, 0, 0);
+    printf("TRACE dbg=%d mask=%d: clocks relative to the first S issue of issuer 0\n", dbg, (int)with_mask);
+    printf("step | iss0: S PV0 PV1 | iss1: S PV0 PV1 | warp(w0h0): wait_s got_s ld_done max_done got_odone exp_done pfull | warp(w0h1) ... | warp(w1h0) ...\n");
+    for (int s_ = 8; s_ < 14; ++s_) {
+      printf("%3d |", s_);
+      for (int a = 3; a < 5; ++a) printf(" %7lld %7lld %7lld |", at(a, s_, 0) - t0, at(a, s_, 1) - t0, at(a, s_, 2) - t0);
+      for (int a = 0; a < 3; ++a) {
+        for (int e = 0; e < 7; ++e) printf(" %7lld", at(a, s_, e) - t0);
+        printf(" |");
+      }
+      printf("\n");
+    }
+    // average phase lengths over steps 8..55 for the first warp
+    for (int a = 0; a < 8; ++a) {
+      if (a == 3 || a == 4) continue;
+      double d[7] = {0};
+      int cnt = 0;
+      for (int s_ = 8; s_ < 56; ++s_, ++cnt) {
+        d[0] += at(a, s_, 1) - at(a, s_, 0);   // waiting for S
+        d[1] += at(a, s_, 2) - at(a, s_, 1);   // TMEM load + s_empty arrive
+        d[2] += at(a, s_, 3) - at(a, s_, 2);   // max
+        d[3] += at(a, s_, 4) - at(a, s_, 3);   // waiting for o_done
+        d[4] += at(a, s_, 5) - at(a, s_, 4);   // (rescale) + exp + pack + st.shared
+        d[5] += at(a, s_, 6) - at(a, s_, 5);   // fences + p_full arrive
+        d[6] += at(a, s_ + 1, 0) - at(a, s_, 0);  // whole step
+      }
+      printf("TRACE-AVG actor %d: wait_S %.0f  ld %.0f  max %.0f  wait_odone %.0f  exp+st %.0f  fence+arrive %.0f  | step %.0f clk\n",
+             a, d[0] / cnt, d[1] / cnt, d[2] / cnt, d[3] / cnt, d[4] / cnt, d[5] / cnt, d[6] / cnt);
+    }
+    {  // skew between the four lane quadrants of stream (w0, h0): ld_done and p_full arrive relative to q = 0
+      const int qa[4] = {0, 5, 6, 7};
+      for (int e : {2, 6}) {
+        double sk[4] = {0};
+        int cnt = 0;
+        for (int s_ = 8; s_ < 56; ++s_, ++cnt)
+          for (int q = 0; q < 4; ++q) sk[q] += at(qa[q], s_, e) - at(0, s_, e);
+        printf("TRACE-SKEW event %d (2 = S loaded, 6 = P staged) of q1 q2 q3 vs q0: %.0f %.0f %.0f clk\n", e, sk[1] / cnt,
+               sk[2] / cnt, sk[3] / cnt);
+      }
+    }
+    {
+      double sS = 0, sPV0 = 0, sPV1 = 0, lat_s = 0, lat_pv = 0;
+      int cnt = 0;
+      for (int s_ = 8; s_ < 56; ++s_, ++cnt) {
+        sS += at(3, s_ + 1, 0) - at(3, s_, 0);
+        // S(j) issue -> softmax warp 0 sees s_full(j)
+        lat_s += at(0, s_, 1) - at(3, s_, 0);
+        // p_full arrive of warp 0 (step j) -> PV0(j) issued ; PV0(j) issued -> o_done seen by warp 0 in step j+1
+        sPV0 += at(3, s_, 1) - at(0, s_, 6);
+        lat_pv += at(0, s_ + 1, 4) - at(3, s_, 1);
+        sPV1 += at(3, s_, 2) - at(3, s_, 1);
+      }
+      printf("TRACE-AVG issuer 0: S period %.0f  | S issue -> warp sees S %.0f | warp p_full arrive -> PV0 issue %.0f | PV0 issue -> warp sees o_done %.0f | PV1 - PV0 issue %.0f\n",
+             sS / cnt, lat_s / cnt, sPV0 / cnt, lat_pv / cnt, sPV1 / cnt);
+    }
+    return 0;
+  }
+  if (mode == "perfall") {  // timing only, all three kernels, with and without a (zero) bit mask
+    perf_case(DDP_BF16, 16, 8192, 8192, 64, false, 5);
+    perf_case(DDP_BF16, 16, 8192, 8192, 64, true, 5);
+    perf_bwd(DDP_BF16, 16, 8192, 8192, 64, 5);
+    perf_bwd(DDP_BF16, 16, 8192, 8192, 64, 5, true);
+    return 0;
   }
   if (mode != "perf" && mode != "bwd" && mode != "bwdfull" && mode != "prof" && mode != "multi") {
     const int bf = DDP_BF16;

@@ -276,7 +276,12 @@ class _AttentionCore(torch.autograd.Function):
         g4 = _heads(grad_out, h)
         k4, q4, v4 = _heads(keys, h), _heads(queries, h), _heads(values, h)
         b, tn, hd = grad_out.shape
-        fused = FUSE_SOFTMAX_BWD and (probs.stride(-2) * probs.element_size()) % 16 == 0
+        from distributed_dot_product.parallel import runtime
+        world = runtime.get_world_size()
+        # the fused epilogue reads P through a TMA map: P rows must be 16-byte aligned and, across ranks, every
+        # rank segment (T/N columns) must start on 16 bytes (ddp_gemm_ex refuses anything else with -2)
+        fused = (FUSE_SOFTMAX_BWD and (probs.stride(-2) * probs.element_size()) % 16 == 0 and
+                 (world == 1 or (v4.size(-2) * probs.element_size()) % 16 == 0))
         if fused:
             # delta_i = sum_j P_ij dP_ij = sum_d dO_id O_id: a [B*Tn*H, d] row dot instead of a slab pass
             delta = _rowdot(grad_out.view(b * tn * h, hd // h), out.view(b * tn * h, hd // h))

@@ -152,7 +152,14 @@ int ddp_attn_bwd_cols(const ddp_tensor* A, const ddp_tensor* G, const ddp_tensor
 size_t ddp_attn_mask_words(int64_t b1, int64_t rows, int64_t cols, int transposed);
 int ddp_attn_pack_mask(const uint8_t* mask, int64_t b1, int64_t rows, int64_t cols, int64_t mask_ld, int64_t mask_sb1,
                        uint32_t* bits, int transposed, void* stream);
-int ddp_debug_timeout_site_attn(void); /* pipeline watchdog of the attention kernels (sites 11-40) */
+int ddp_debug_timeout_site_attn(void); /* pipeline watchdog of the attention kernels (sites 11-49) */
+/* Pipeline trace of ddp_attn_fwd (a profiling aid; the reference has only the `measure` printout,
+ * multiplication/functions.py:24-41): while `device_buf` is non-null, CTA 0 of every forward launch stores
+ * clock64() stamps of the first `steps` column steps of its first work item as [actors][steps][events] int64
+ * (actors 0-2 and 5-7: softmax warps, 3-4: the two MMA issuers; events: see attn_fwd_sm100.cuh).  Pass NULL to
+ * switch it off again.  Not thread safe; tools/trace_attn.py and `attn_harness trace` print the table. */
+void ddp_attn_debug_trace(long long* device_buf);
+int ddp_attn_debug_trace_dims(int* actors, int* steps, int* events);
 
 /* Row softmax over the last dim of x[b1][b0][rows][cols] with fused scale and boolean mask:
  *   y = softmax(scale * x  masked_fill(mask, -inf))     (reference: module.py:65-67)

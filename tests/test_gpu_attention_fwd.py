@@ -174,3 +174,61 @@ def test_packed_mask_cache_follows_mask_contents(cuda_device):
                       heads, scale)
     assert (o2 - ref2).abs().max().item() <= 2e-2 * max(1.0, ref2.abs().max().item())
     assert torch.equal(o3, o1)
+
+
+def test_attention_harness_more_items_than_ctas(cuda_device):
+    """160 work items on 148 CTAs (csrc/tests/attn_harness.cu, mode multi): every barrier phase, ring slot and
+    step counter of the three attention kernels is carried from one work item into the next and checked element
+    by element against a double-precision CPU reference."""
+    exe = os.path.join(ROOT, 'build', 'attn_harness')
+    if not os.path.exists(exe):
+        subprocess.check_call(['python', os.path.join(ROOT, 'build.py'), 'harness'], cwd=ROOT)
+    r = subprocess.run([exe, 'multi'], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=900)
+    tail = '\n'.join(r.stdout.splitlines()[-20:])
+    assert r.returncode == 0, tail
+    assert 'fail=0' in r.stdout, tail
+
+
+@pytest.mark.parametrize('mask_kind', ['random', 'causal'])
+def test_flash_training_many_items_per_cta(cuda_device, mask_kind):
+    """The flagship head shape at 256 work items per kernel (16 heads x 4096 rows = 256 row-block pairs on 148
+    CTAs, so most CTAs run a second item): output and the three input gradients of the slab-free path, element
+    by element, against a plain PyTorch fp32 reference (reference semantics: module.py:61-69 + autograd)."""
+    import distributed_dot_product.ops.attention as att
+    torch.manual_seed(6)
+    b, heads, tn, d = 1, 16, 4096, 64
+    k = torch.randn(b, tn, heads * d, device=cuda_device).to(torch.bfloat16)
+    q = torch.randn(b, tn, heads * d, device=cuda_device).to(torch.bfloat16)
+    v = torch.randn(b, tn, heads * d, device=cuda_device).to(torch.bfloat16)
+    g = torch.randn(b, tn, heads * d, device=cuda_device).to(torch.bfloat16)
+    if mask_kind == 'random':
+        mask = torch.rand(b, tn, tn, device=cuda_device) < 0.3
+    else:
+        mask = torch.triu(torch.ones(tn, tn, dtype=torch.bool, device=cuda_device), diagonal=1).unsqueeze(0)
+    scale = 1.0 / math.sqrt(d)
+    assert att.FLASH_TRAIN
+    kk, qq, vv = (t.clone().requires_grad_(True) for t in (k, q, v))
+    from distributed_dot_product import _native
+    before = _native.launch_count
+    out = att.attention_core(kk, qq, vv, mask, heads, scale, 64)
+    out.backward(g)
+    assert _native.launch_count - before <= 6  # pack x2, fwd, rowdot, bwd rows, bwd cols: the slab-free path ran
+    got = (out.detach().float(), kk.grad.float(), qq.grad.float(), vv.grad.float())
+    # fp32 reference, one head at a time (a [16, 4096, 4096] fp32 slab per tensor would also fit, but why)
+    ref = [torch.zeros(b, tn, heads * d, device=cuda_device) for _ in range(4)]
+    for h in range(heads):
+        sl = slice(h * d, (h + 1) * d)
+        kf, qf, vf = (t[..., sl].float().requires_grad_(True) for t in (k, q, v))
+        s_ = (kf @ qf.transpose(-1, -2)) * scale
+        s_ = s_.masked_fill(mask, float('-inf'))
+        o = torch.softmax(s_, dim=-1) @ vf
+        o.backward(g[..., sl].float())
+        for dst, src in zip(ref, (o.detach(), kf.grad, qf.grad, vf.grad)):
+            dst[..., sl] = src
+    for name, f, r in zip(('out', 'dK', 'dQ', 'dV'), got, ref):
+        err = (f - r).abs().max().item()
+        bound = 3e-2 * max(1.0, r.abs().max().item())
+        assert err <= bound, (name, mask_kind, err, bound)
+        # a wrong 128-row block would leave the max error small relative to a large tensor: also check per block
+        blk = (f - r).abs().view(b, tn // 128, 128, heads, d).amax(dim=(2, 4))
+        assert blk.max().item() <= bound, (name, mask_kind, 'block', blk.max().item())

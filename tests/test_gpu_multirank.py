@@ -135,3 +135,110 @@ def test_module_flash_multi_gpu(world):
     if _ngpu() < world:
         pytest.skip('needs %d GPUs' % world)
     run_distributed(_module_flash, world, use_cuda=True, timeout=150)
+
+
+def _module_flash_dense_twin(rank, world):
+    """bf16 slab-free path against the fp32 DENSE twin (``distributed=False`` on the gathered inputs), the check of
+    the reference's tests/test_gradient.py:90-121 on the path the benchmark runs: output, input gradients and the
+    all-reduced parameter gradients, a random 30 % mask and a causal mask, two steps each (workspace parities)."""
+    import torch.distributed as dist
+    import distributed_dot_product.ops.attention as att
+    from distributed_dot_product import _native
+    from distributed_dot_product.module import DistributedDotProductAttn
+    from distributed_dot_product.parallel import allreduce_gradients, broadcast_parameters
+    from distributed_dot_product.parallel.runtime import check_status
+    dev = torch.device('cuda', torch.cuda.current_device())
+    torch.manual_seed(21)
+    dim, tn, heads = 512, 384, 8
+    model = DistributedDotProductAttn(dim, num_heads=heads, offset=64).to(dev)
+    broadcast_parameters(model)
+    twin = DistributedDotProductAttn(dim, num_heads=heads, distributed=False).to(dev)
+    twin.load_state_dict(model.state_dict())
+    model = model.to(torch.bfloat16)
+    # the twin computes in fp32 from the SAME (bf16-rounded) weights
+    twin.load_state_dict({n: t.float() for n, t in model.state_dict().items()})
+    t = tn * world
+    rows = slice(rank * tn, (rank + 1) * tn)
+    assert att.FLASH_TRAIN
+
+    def gather(x):
+        parts = [torch.empty_like(x) for _ in range(world)]
+        dist.all_gather(parts, x.detach().contiguous())
+        return torch.cat(parts, dim=1)
+
+    def rel(a, b):
+        return (a.float() - b.float()).abs().max().item() / (b.float().abs().max().item() + 1e-12)
+
+    for kind in ('random', 'causal'):
+        for step in range(2):
+            torch.manual_seed(100 + 10 * step + rank)
+            k = (0.5 * torch.randn(1, tn, dim, device=dev)).to(torch.bfloat16).requires_grad_(True)
+            q = (0.5 * torch.randn(1, tn, dim, device=dev)).to(torch.bfloat16).requires_grad_(True)
+            if kind == 'random':
+                torch.manual_seed(300 + step)   # the same global mask on every rank
+                gmask = torch.rand(1, t, t, device=dev) < 0.3
+            else:
+                gmask = torch.triu(torch.ones(t, t, dtype=torch.bool, device=dev), diagonal=1).unsqueeze(0)
+            model.zero_grad()
+            twin.zero_grad()
+            before = _native.launch_count
+            out = model(k, q, k, gmask[:, rows].contiguous())
+            out.float().sum().backward()
+            check_status()
+            kg, qg = gather(k).float().requires_grad_(True), gather(q).float().requires_grad_(True)
+            ref = twin(kg, qg, kg, gmask)
+            ref.sum().backward()
+            errs = {'out': rel(out, ref[:, rows]), 'k.grad': rel(k.grad, kg.grad[:, rows]),
+                    'q.grad': rel(q.grad, qg.grad[:, rows])}
+            assert all(v < 3e-2 for v in errs.values()), (kind, step, errs)
+            allreduce_gradients(model)
+            gscale = max(pr.grad.abs().max().item() for pr in twin.parameters())
+            for (n, p), (_, pr) in zip(model.named_parameters(), twin.named_parameters()):
+                e = (p.grad.float() - pr.grad).abs().max().item() / max(pr.grad.abs().max().item(), 0.05 * gscale)
+                assert e < 4e-2, (kind, step, n, e)
+
+
+@pytest.mark.parametrize('world', [2, 4, 8])
+def test_module_flash_dense_twin_multi_gpu(world):
+    if _ngpu() < world:
+        pytest.skip('needs %d GPUs' % world)
+    run_distributed(_module_flash_dense_twin, world, use_cuda=True, timeout=200)
+
+
+def _module_ragged_slab(rank, world):
+    """bf16 layer with T/N = 100 (rows per rank not a multiple of 8 or 32) and a mask: the slab path must pick
+    the unfused softmax backward (the fused epilogue needs 16-byte aligned rank segments) instead of raising."""
+    import torch.distributed as dist
+    from distributed_dot_product.module import DistributedDotProductAttn
+    from distributed_dot_product.parallel import broadcast_parameters
+    dev = torch.device('cuda', torch.cuda.current_device())
+    torch.manual_seed(31)
+    dim, tn, heads = 128, 100, 2
+    model = DistributedDotProductAttn(dim, num_heads=heads, offset=32).to(dev)
+    broadcast_parameters(model)
+    twin = DistributedDotProductAttn(dim, num_heads=heads, distributed=False).to(dev)
+    model = model.to(torch.bfloat16)
+    twin.load_state_dict({n: t.float() for n, t in model.state_dict().items()})
+    t = tn * world
+    rows = slice(rank * tn, (rank + 1) * tn)
+    torch.manual_seed(32)
+    gmask = torch.rand(1, t, t, device=dev) < 0.2
+    torch.manual_seed(33 + rank)
+    x = (0.5 * torch.randn(1, tn, dim, device=dev)).to(torch.bfloat16).requires_grad_(True)
+    out = model(x, x, x, gmask[:, rows].contiguous())
+    out.float().sum().backward()
+    parts = [torch.empty_like(x) for _ in range(world)]
+    dist.all_gather(parts, x.detach().contiguous())
+    xg = torch.cat(parts, dim=1).float().requires_grad_(True)
+    ref = twin(xg, xg, xg, gmask)
+    ref.sum().backward()
+    for name, a, b in (('out', out, ref[:, rows]), ('x.grad', x.grad, xg.grad[:, rows])):
+        e = (a.float() - b).abs().max().item() / (b.abs().max().item() + 1e-12)
+        assert e < 4e-2, (name, e)
+
+
+@pytest.mark.parametrize('world', [2])
+def test_module_ragged_rows_multi_gpu(world):
+    if _ngpu() < world:
+        pytest.skip('needs %d GPUs' % world)
+    run_distributed(_module_ragged_slab, world, use_cuda=True, timeout=200)
