@@ -9,6 +9,7 @@
 #include "../common/host_util.h"
 #include "../gemm/tma_map.h"
 #include "attn_bwd_sm100.cuh"
+#include "attn_fwd2_sm100.cuh"
 
 namespace ddp {
 
@@ -53,6 +54,28 @@ static int attn_env_dbg() {
 }
 
 static long long* g_attn_trace = nullptr;  // ddp_attn_debug_trace
+
+constexpr int kAt2Stages = 4;
+constexpr int kAt2Smem = 2 * kAtTile + kAt2StageO + kAt2Stages * kAt2StageBytes + (2 * kAt2Stages + 22) * 8 + 16 + 4 * 128 * 8 + 1024;
+static_assert(kAt2Smem <= 232448, "shared memory budget exceeded");
+
+// Second-generation forward (P stays in tensor memory), see attn_fwd2_sm100.cuh.
+template <int DT>
+static int attn_launch2(const AttnKParams& p, int grid, cudaStream_t stream) {
+  auto kern = (p.dbg & 1) ? attn_fwd2_kernel<DT, kAt2Stages, true> : attn_fwd2_kernel<DT, kAt2Stages, false>;
+  static bool configured[2][64] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 64 && !configured[p.dbg & 1][dev]) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kAt2Smem);
+    if (e != cudaSuccess) return set_error(-12, cudaGetErrorString(e));
+    configured[p.dbg & 1][dev] = true;
+  }
+  kern<<<grid, kAtThreads, kAt2Smem, stream>>>(p);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return set_error(-13, cudaGetErrorString(e));
+  return 0;
+}
 
 template <int DT>
 static int attn_launch(const AttnKParams& p, int grid, cudaStream_t stream) {
@@ -187,6 +210,8 @@ extern "C" int ddp_attn_fwd(const ddp_tensor* A, const ddp_tensor* B, const ddp_
   const int sms = ddp_num_sms();
   int grid = world > 1 ? sms : (int)(items < sms ? items : sms);
   if (grid < 1) grid = 1;
+  if (!(p.dbg & 64))  // dbg bit 64: the first-generation kernel (P staged through shared memory)
+    return dt == DDP_BF16 ? attn_launch2<DDP_BF16>(p, grid, stream) : attn_launch2<DDP_F16>(p, grid, stream);
   return dt == DDP_BF16 ? attn_launch<DDP_BF16>(p, grid, stream) : attn_launch<DDP_F16>(p, grid, stream);
 }
 
