@@ -56,7 +56,7 @@ static int attn_env_dbg() {
 static long long* g_attn_trace = nullptr;  // ddp_attn_debug_trace
 
 constexpr int kAt2Stages = 4;
-constexpr int kAt2Smem = 2 * kAtTile + kAt2StageO + kAt2Stages * kAt2StageBytes + (2 * kAt2Stages + 22) * 8 + 16 + 4 * 128 * 8 + 1024;
+constexpr int kAt2Smem = 2 * kAtTile + kAt2StageO + kAt2Stages * kAt2StageBytes + (2 * kAt2Stages + 26) * 8 + 16 + 4 * 128 * 8 + 1024;
 static_assert(kAt2Smem <= 232448, "shared memory budget exceeded");
 
 // Second-generation forward (P stays in tensor memory), see attn_fwd2_sm100.cuh.

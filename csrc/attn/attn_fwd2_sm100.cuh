@@ -52,7 +52,8 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_fwd2_kernel(const __grid_c
   uint64_t* s_full = a_empty + 1;           // [8]  sub-tile w*4 + c of S landed in TMEM
   uint64_t* p_full = s_full + 8;            // [8]  its P written over it (and O_wh rescaled)
   uint64_t* o_done = p_full + 8;            // [4]  an O_wh += P V product finished (two per step and stream)
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_done + 4);
+  uint64_t* o_final = o_done + 4;           // [4]  the LAST product of the work item into O_wh finished
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_final + 4);
   float2* sStat = reinterpret_cast<float2*>(tmem_slot + 4);  // [2][2][128] (max, sum) of every stream, for the merge
 
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);  // warp-uniform for the compiler, too
@@ -85,7 +86,10 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_fwd2_kernel(const __grid_c
       mbar_init(&s_full[i], 1);
       mbar_init(&p_full[i], 4);
     }
-    for (int st = 0; st < 4; ++st) mbar_init(&o_done[st], 1);
+    for (int st = 0; st < 4; ++st) {
+      mbar_init(&o_done[st], 1);
+      mbar_init(&o_final[st], 1);
+    }
     fence_mbar_init();
   }
   if (warp == 2) tmem_alloc(tmem_slot, kAtTmemCols);
@@ -232,6 +236,7 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_fwd2_kernel(const __grid_c
               for (int kk = 0; kk < 2; ++kk)
                 umma_ts(tO_w + h * 64, tS_w + c * 32 + kk * 8, dv + 128 * kk, kIdO, (j | sub | kk) != 0 ? 1u : 0u);
               umma_commit(&o_done[w * 2 + h]);
+              if (!more && sub == 1) umma_commit(&o_final[w * 2 + h]);
             }
             __syncwarp();
             if (more) issue_s(nslot, c);
@@ -326,7 +331,7 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_fwd2_kernel(const __grid_c
     const bool has_mask = p.mask_bits != nullptr;
     // this thread's two mask words of a step inside the stage's mask tile
     const uint32_t mask_off = smem_u32(sKV) + kAtStageBytes + (w * 4 + q) * 512 + (h * 2) * 128 + lane * 4;
-    uint32_t sf_ph = 0;
+    uint32_t sf_ph = 0, of_ph = 0;
     uint32_t npv = 0;                // O_st += P V products issued for this stream so far (two per step)
     uint32_t slot = 0, slot_ph = 0;  // ring position of the current step (for the mask tile)
     for (int it = blockIdx.x; it < items; it += gridDim.x) {
@@ -457,7 +462,10 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_fwd2_kernel(const __grid_c
         sf_ph ^= 1;
       }
       // ---- row block finished: merge the two column-half streams of every row, O = (Oa fa + Ob fb) / l
-      mbar_wait(&o_done[st], (npv - 1u) & 1u, 59);
+      // (o_done cannot be used here: two of its phases may still be outstanding, which a parity wait cannot tell
+      //  from none; inside the step loop the s_full wait in front of the rescale bounds it to one)
+      mbar_wait(&o_final[st], of_ph, 59);
+      of_ph ^= 1;
       tc_fence_after();
       sStat[(w * 2 + h) * kAtBM + row_in] = make_float2(m_used, l);
       tc_fence_before();
