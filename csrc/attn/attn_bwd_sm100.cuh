@@ -181,7 +181,7 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd_rows_kernel(const __gr
   uint64_t* o_done = p_full + 2;     // [2] dA_w += dS_w B_j finished
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_done + 2);
 
-  const int warp = (p.dbg & 8) ? ((threadIdx.x >> 5) + 4) % (kAtThreads / 32) : (threadIdx.x >> 5);  // see the forward kernel
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);  // warp-uniform for the compiler, too
   const int lane = threadIdx.x & 31;
   const int Bt = p.b0 * p.b1;
   const bool dist = p.world > 1;
@@ -281,107 +281,69 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd_rows_kernel(const __gr
         }
       }
     } else if (warp == 1 || warp == 3) {
-      // ===================================================== MMA issuers (event driven): warp 1 -> w = 0, warp 3 -> w = 1
-      if (lane == 0) {
+      // ===================================================== MMA issuers: warp 1 -> w = 0, warp 3 -> w = 1
+      // Static schedule in the order the events arrive in steady state - [S, dP of step j+1 as soon as the
+      // elementwise warps hold those of step j] [dA += dS_j B_j once dS_j is staged] - walked by the WHOLE warp
+      // (blocking waits included) with one elected lane issuing.  Warp-uniform operands keep the MMA descriptors
+      // in uniform registers; issued from inside `if (lane == 0)` every tcgen05.mma was wrapped in an
+      // elect / R2UR / branch loop of ~14 dependent instructions, ~100 clk per MMA and 12 MMAs per step here.
+      {
         constexpr uint32_t kIdS = umma_idesc(DT, 0u, 0u, kAtBM, kAbStep);  // S, dP: A K-major, B K-major, N = 64
         constexpr uint32_t kIdA = umma_idesc(DT, 0u, 1u, kAtBM, 64);       // dA: A = dS K-major, B = B_j MN-major
+        const bool leader = elect_one();
         const int w = (warp == 1) ? 0 : 1;
         uint32_t a_ph = 0, se_ph = 0, pf_ph = 0;
         const uint32_t sKV_u = smem_u32(sKV);
         const uint32_t tS_w = tmem_base + w * 64, tP_w = tmem_base + 128 + w * 64, tA_w = tmem_base + 256 + w * 64;
-        uint64_t dA[4], dG[4], dD[4];  // the operands that do not move: A_w, dO_w, dS_w (4 k-slices each)
+        const uint64_t dA0 = umma_smem_desc(smem_u32(sA) + w * kAtTile, 16, 1024);   // the operands that do not move
+        const uint64_t dG0 = umma_smem_desc(smem_u32(sG) + w * kAtTile, 16, 1024);
+        const uint64_t dD0 = umma_smem_desc(smem_u32(sDS) + w * kAtTile, 16, 1024);
+        uint32_t slot = 0, slot_ph = 0;  // ring position of the next S / dP step to issue
+        auto issue_s = [&]() {
+          mbar_wait(&kv_full[slot], slot_ph, 44);
+          mbar_wait(&s_empty[w], se_ph ^ 1, 45);
+          se_ph ^= 1;
+          tc_fence_after();
+          const uint64_t db = umma_smem_desc(sKV_u + slot * kStage, 16, 1024);
+          const uint64_t dv = umma_smem_desc(sKV_u + slot * kStage + kAbHalfTile, 16, 1024);
+          if (leader) {
 #pragma unroll
-        for (int kk = 0; kk < 4; ++kk) {
-          dA[kk] = umma_smem_desc(smem_u32(sA) + w * kAtTile + kk * 32, 16, 1024);
-          dG[kk] = umma_smem_desc(smem_u32(sG) + w * kAtTile + kk * 32, 16, 1024);
-          dD[kk] = umma_smem_desc(smem_u32(sDS) + w * kAtTile + kk * 32, 16, 1024);
-        }
-        uint32_t g0 = 0;
-        const bool poll_test = (p.dbg & 2) != 0;  // see the forward kernel: dbg bit 2 / bit 4
-        auto poll = [&](uint64_t* bar, uint32_t parity) {
-          return poll_test ? mbar_test_wait(bar, parity) : mbar_try_wait(bar, parity);
-        };
-        if (p.dbg & 4) {
-          for (int it = blockIdx.x; it < items; it += gridDim.x) {
-            mbar_wait(a_full, a_ph, 24);
-            a_ph ^= 1;
-            tc_fence_after();
-            auto issue_s = [&](int j) {
-              const uint32_t g = g0 + j;
-              mbar_wait(&kv_full[g % STAGES], (g / STAGES) & 1, 44);
-              mbar_wait(&s_empty[w], se_ph ^ 1, 45);
-              se_ph ^= 1;
-              tc_fence_after();
-              const uint64_t db = umma_smem_desc(sKV_u + (g % STAGES) * kStage, 16, 1024);
-              const uint64_t dv = umma_smem_desc(sKV_u + (g % STAGES) * kStage + kAbHalfTile, 16, 1024);
+            for (int kk = 0; kk < 4; ++kk) umma_ss<false>(tS_w, dA0 + 2 * kk, db + 2 * kk, kIdS, kk != 0 ? 1u : 0u);
 #pragma unroll
-              for (int kk = 0; kk < 4; ++kk) umma_ss<false>(tS_w, dA[kk], db + 2 * kk, kIdS, kk != 0 ? 1u : 0u);
-#pragma unroll
-              for (int kk = 0; kk < 4; ++kk) umma_ss<false>(tP_w, dG[kk], dv + 2 * kk, kIdS, kk != 0 ? 1u : 0u);
-              umma_commit(&s_full[w]);
-            };
-            issue_s(0);
-            for (int j = 0; j < nj; ++j) {
-              if (j + 1 < nj) issue_s(j + 1);
-              const uint32_t g = g0 + j;
-              mbar_wait(&p_full[w], pf_ph, 46);
-              pf_ph ^= 1;
-              tc_fence_after();
-              const uint64_t db = umma_smem_desc(sKV_u + (g % STAGES) * kStage, kAbHalfTile, 1024, 2);
-#pragma unroll
-              for (int kk = 0; kk < 4; ++kk)
-                umma_ss<false>(tA_w, dD[kk], db + 128 * kk, kIdA, (j | kk) != 0 ? 1u : 0u);
-              umma_commit(&o_done[w]);
-              umma_commit(&kv_empty[g % STAGES]);
-            }
-            umma_commit(a_empty);
-            g0 += static_cast<uint32_t>(nj);
+            for (int kk = 0; kk < 4; ++kk) umma_ss<false>(tP_w, dG0 + 2 * kk, dv + 2 * kk, kIdS, kk != 0 ? 1u : 0u);
+            umma_commit(&s_full[w]);
           }
-        } else
+          __syncwarp();
+          if (++slot == STAGES) {
+            slot = 0;
+            slot_ph ^= 1;
+          }
+        };
+        uint32_t pslot = 0;  // ring position of the next dA product
         for (int it = blockIdx.x; it < items; it += gridDim.x) {
           mbar_wait(a_full, a_ph, 24);
           a_ph ^= 1;
           tc_fence_after();
-          int nS = 0, nPV = 0, kvr = 0;
-          uint32_t spins = 0;
-          uint64_t t0 = 0;
-          while (nPV < nj) {
-            bool progress = false;
-            if (nS < nj) {
-              const uint32_t g = g0 + nS;
-              if (nS >= kvr && poll(&kv_full[g % STAGES], (g / STAGES) & 1)) kvr = nS + 1;
-              if (nS < kvr && poll(&s_empty[w], se_ph ^ 1)) {
-                se_ph ^= 1;
-                tc_fence_after();
-                const uint64_t db = umma_smem_desc(sKV_u + (g % STAGES) * kStage, 16, 1024);
-                const uint64_t dv = umma_smem_desc(sKV_u + (g % STAGES) * kStage + kAbHalfTile, 16, 1024);
-#pragma unroll
-                for (int kk = 0; kk < 4; ++kk) umma_ss<false>(tS_w, dA[kk], db + 2 * kk, kIdS, kk != 0 ? 1u : 0u);
-#pragma unroll
-                for (int kk = 0; kk < 4; ++kk) umma_ss<false>(tP_w, dG[kk], dv + 2 * kk, kIdS, kk != 0 ? 1u : 0u);
-                umma_commit(&s_full[w]);
-                ++nS;
-                progress = true;
-              }
-            }
-            if (nPV < nS && poll(&p_full[w], pf_ph)) {
-              pf_ph ^= 1;
-              tc_fence_after();
-              const uint32_t g = g0 + nPV;
-              // B_j as [K = j][N = d], MN-major
-              const uint64_t db = umma_smem_desc(sKV_u + (g % STAGES) * kStage, kAbHalfTile, 1024, 2);
+          issue_s();
+          for (int j = 0; j < nj; ++j) {
+            if (j + 1 < nj) issue_s();
+            mbar_wait(&p_full[w], pf_ph, 46);
+            pf_ph ^= 1;
+            tc_fence_after();
+            // B_j as [K = j][N = d], MN-major
+            const uint64_t db = umma_smem_desc(sKV_u + pslot * kStage, kAbHalfTile, 1024, 2);
+            if (leader) {
 #pragma unroll
               for (int kk = 0; kk < 4; ++kk)
-                umma_ss<false>(tA_w, dD[kk], db + 128 * kk, kIdA, (nPV | kk) != 0 ? 1u : 0u);
+                umma_ss<false>(tA_w, dD0 + 2 * kk, db + 128 * kk, kIdA, (j | kk) != 0 ? 1u : 0u);
               umma_commit(&o_done[w]);
-              umma_commit(&kv_empty[g % STAGES]);  // one of the two arrivals that free the ring slot
-              ++nPV;
-              progress = true;
+              umma_commit(&kv_empty[pslot]);  // one of the two arrivals that free the ring slot
             }
-            if (attn_issuer_watchdog(progress, spins, t0, 26u)) break;
+            __syncwarp();
+            if (++pslot == STAGES) pslot = 0;
           }
-          umma_commit(a_empty);
-          g0 += static_cast<uint32_t>(nj);
+          if (leader) umma_commit(a_empty);
+          __syncwarp();
         }
       }
     } else {
@@ -575,7 +537,7 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd_cols_kernel(const __gr
   uint64_t* o_done = p_full + 2;     // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_done + 2);
 
-  const int warp = (p.dbg & 8) ? ((threadIdx.x >> 5) + 4) % (kAtThreads / 32) : (threadIdx.x >> 5);  // see the forward kernel
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);  // warp-uniform for the compiler, too
   const int lane = threadIdx.x & 31;
   const int Bt = p.b0 * p.b1;
   const bool dist = p.world > 1;
@@ -681,116 +643,71 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd_cols_kernel(const __gr
         }
       }
     } else if (warp == 1 || warp == 3) {
-      // ===================================================== MMA issuers (event driven): warp 1 -> w = 0, warp 3 -> w = 1
-      if (lane == 0) {
+      // ===================================================== MMA issuers: warp 1 -> w = 0, warp 3 -> w = 1
+      // Static schedule walked by the whole warp, one elected lane issues (see the row-side kernel): 16 MMAs per
+      // step and column block here.
+      {
         constexpr uint32_t kIdS = umma_idesc(DT, 0u, 0u, kAtBM, kAbStep);  // S^T, dP^T
         constexpr uint32_t kIdO = umma_idesc(DT, 0u, 1u, kAtBM, 64);       // dV, dB: B operand MN-major
+        const bool leader = elect_one();
         const int w = (warp == 1) ? 0 : 1;
         uint32_t a_ph = 0, se_ph = 0, pf_ph = 0;
         const uint32_t sKV_u = smem_u32(sKV);
         const uint32_t tS_w = tmem_base + w * 64, tP_w = tmem_base + 128 + w * 64, tV_w = tmem_base + 256 + w * 64,
                        tB_w = tmem_base + 384 + w * 64;
-        uint64_t dB_[4], dV_[4], dPt[4], dDt[4];  // the operands that do not move (4 k-slices each)
+        const uint64_t dB0 = umma_smem_desc(smem_u32(sB) + w * kAtTile, 16, 1024);  // the operands that do not move
+        const uint64_t dV0 = umma_smem_desc(smem_u32(sV) + w * kAtTile, 16, 1024);
+        const uint64_t dPt0 = umma_smem_desc(smem_u32(sPt) + w * kAtTile, 16, 1024);
+        const uint64_t dDt0 = umma_smem_desc(smem_u32(sDt) + w * kAtTile, 16, 1024);
+        uint32_t slot = 0, slot_ph = 0;
+        auto issue_s = [&]() {
+          mbar_wait(&kv_full[slot], slot_ph, 47);
+          mbar_wait(&s_empty[w], se_ph ^ 1, 48);
+          se_ph ^= 1;
+          tc_fence_after();
+          const uint64_t da = umma_smem_desc(sKV_u + slot * kAbColsStage, 16, 1024);
+          const uint64_t dg = umma_smem_desc(sKV_u + slot * kAbColsStage + kAbHalfTile, 16, 1024);
+          if (leader) {
 #pragma unroll
-        for (int kk = 0; kk < 4; ++kk) {
-          dB_[kk] = umma_smem_desc(smem_u32(sB) + w * kAtTile + kk * 32, 16, 1024);
-          dV_[kk] = umma_smem_desc(smem_u32(sV) + w * kAtTile + kk * 32, 16, 1024);
-          dPt[kk] = umma_smem_desc(smem_u32(sPt) + w * kAtTile + kk * 32, 16, 1024);
-          dDt[kk] = umma_smem_desc(smem_u32(sDt) + w * kAtTile + kk * 32, 16, 1024);
-        }
-        uint32_t g0 = 0;
-        const bool poll_test = (p.dbg & 2) != 0;  // see the forward kernel: dbg bit 2 / bit 4
-        auto poll = [&](uint64_t* bar, uint32_t parity) {
-          return poll_test ? mbar_test_wait(bar, parity) : mbar_try_wait(bar, parity);
-        };
-        if (p.dbg & 4) {
-          for (int it = blockIdx.x; it < items; it += gridDim.x) {
-            mbar_wait(a_full, a_ph, 34);
-            a_ph ^= 1;
-            tc_fence_after();
-            auto issue_s = [&](int j) {
-              const uint32_t g = g0 + j;
-              mbar_wait(&kv_full[g % STAGES], (g / STAGES) & 1, 47);
-              mbar_wait(&s_empty[w], se_ph ^ 1, 48);
-              se_ph ^= 1;
-              tc_fence_after();
-              const uint64_t da = umma_smem_desc(sKV_u + (g % STAGES) * kAbColsStage, 16, 1024);
-              const uint64_t dg = umma_smem_desc(sKV_u + (g % STAGES) * kAbColsStage + kAbHalfTile, 16, 1024);
+            for (int kk = 0; kk < 4; ++kk) umma_ss<false>(tS_w, dB0 + 2 * kk, da + 2 * kk, kIdS, kk != 0 ? 1u : 0u);
 #pragma unroll
-              for (int kk = 0; kk < 4; ++kk) umma_ss<false>(tS_w, dB_[kk], da + 2 * kk, kIdS, kk != 0 ? 1u : 0u);
-#pragma unroll
-              for (int kk = 0; kk < 4; ++kk) umma_ss<false>(tP_w, dV_[kk], dg + 2 * kk, kIdS, kk != 0 ? 1u : 0u);
-              umma_commit(&s_full[w]);
-            };
-            issue_s(0);
-            for (int j = 0; j < nj; ++j) {
-              if (j + 1 < nj) issue_s(j + 1);
-              const uint32_t g = g0 + j;
-              mbar_wait(&p_full[w], pf_ph, 49);
-              pf_ph ^= 1;
-              tc_fence_after();
-              const uint64_t da = umma_smem_desc(sKV_u + (g % STAGES) * kAbColsStage, kAbHalfTile, 1024, 2);
-              const uint64_t dg = umma_smem_desc(sKV_u + (g % STAGES) * kAbColsStage + kAbHalfTile, kAbHalfTile, 1024, 2);
-#pragma unroll
-              for (int kk = 0; kk < 4; ++kk)  // dV_w += P^T_w dO_i
-                umma_ss<false>(tV_w, dPt[kk], dg + 128 * kk, kIdO, (j | kk) != 0 ? 1u : 0u);
-#pragma unroll
-              for (int kk = 0; kk < 4; ++kk)  // dB_w += dS^T_w A_i
-                umma_ss<false>(tB_w, dDt[kk], da + 128 * kk, kIdO, (j | kk) != 0 ? 1u : 0u);
-              umma_commit(&o_done[w]);
-              umma_commit(&kv_empty[g % STAGES]);
-            }
-            umma_commit(a_empty);
-            g0 += static_cast<uint32_t>(nj);
+            for (int kk = 0; kk < 4; ++kk) umma_ss<false>(tP_w, dV0 + 2 * kk, dg + 2 * kk, kIdS, kk != 0 ? 1u : 0u);
+            umma_commit(&s_full[w]);
           }
-        } else
+          __syncwarp();
+          if (++slot == STAGES) {
+            slot = 0;
+            slot_ph ^= 1;
+          }
+        };
+        uint32_t pslot = 0;
         for (int it = blockIdx.x; it < items; it += gridDim.x) {
           mbar_wait(a_full, a_ph, 34);
           a_ph ^= 1;
           tc_fence_after();
-          int nS = 0, nPV = 0, kvr = 0;
-          uint32_t spins = 0;
-          uint64_t t0 = 0;
-          while (nPV < nj) {
-            bool progress = false;
-            if (nS < nj) {
-              const uint32_t g = g0 + nS;
-              if (nS >= kvr && poll(&kv_full[g % STAGES], (g / STAGES) & 1)) kvr = nS + 1;
-              if (nS < kvr && poll(&s_empty[w], se_ph ^ 1)) {
-                se_ph ^= 1;
-                tc_fence_after();
-                const uint64_t da = umma_smem_desc(sKV_u + (g % STAGES) * kAbColsStage, 16, 1024);
-                const uint64_t dg = umma_smem_desc(sKV_u + (g % STAGES) * kAbColsStage + kAbHalfTile, 16, 1024);
-#pragma unroll
-                for (int kk = 0; kk < 4; ++kk) umma_ss<false>(tS_w, dB_[kk], da + 2 * kk, kIdS, kk != 0 ? 1u : 0u);
-#pragma unroll
-                for (int kk = 0; kk < 4; ++kk) umma_ss<false>(tP_w, dV_[kk], dg + 2 * kk, kIdS, kk != 0 ? 1u : 0u);
-                umma_commit(&s_full[w]);
-                ++nS;
-                progress = true;
-              }
-            }
-            if (nPV < nS && poll(&p_full[w], pf_ph)) {
-              pf_ph ^= 1;
-              tc_fence_after();
-              const uint32_t g = g0 + nPV;
-              const uint64_t da = umma_smem_desc(sKV_u + (g % STAGES) * kAbColsStage, kAbHalfTile, 1024, 2);
-              const uint64_t dg = umma_smem_desc(sKV_u + (g % STAGES) * kAbColsStage + kAbHalfTile, kAbHalfTile, 1024, 2);
+          issue_s();
+          for (int j = 0; j < nj; ++j) {
+            if (j + 1 < nj) issue_s();
+            mbar_wait(&p_full[w], pf_ph, 49);
+            pf_ph ^= 1;
+            tc_fence_after();
+            const uint64_t da = umma_smem_desc(sKV_u + pslot * kAbColsStage, kAbHalfTile, 1024, 2);
+            const uint64_t dg = umma_smem_desc(sKV_u + pslot * kAbColsStage + kAbHalfTile, kAbHalfTile, 1024, 2);
+            if (leader) {
 #pragma unroll
               for (int kk = 0; kk < 4; ++kk)  // dV_w += P^T_w dO_i
-                umma_ss<false>(tV_w, dPt[kk], dg + 128 * kk, kIdO, (nPV | kk) != 0 ? 1u : 0u);
+                umma_ss<false>(tV_w, dPt0 + 2 * kk, dg + 128 * kk, kIdO, (j | kk) != 0 ? 1u : 0u);
 #pragma unroll
               for (int kk = 0; kk < 4; ++kk)  // dB_w += dS^T_w A_i
-                umma_ss<false>(tB_w, dDt[kk], da + 128 * kk, kIdO, (nPV | kk) != 0 ? 1u : 0u);
+                umma_ss<false>(tB_w, dDt0 + 2 * kk, da + 128 * kk, kIdO, (j | kk) != 0 ? 1u : 0u);
               umma_commit(&o_done[w]);
-              umma_commit(&kv_empty[g % STAGES]);  // one of the two arrivals that free the ring slot
-              ++nPV;
-              progress = true;
+              umma_commit(&kv_empty[pslot]);  // one of the two arrivals that free the ring slot
             }
-            if (attn_issuer_watchdog(progress, spins, t0, 36u)) break;
+            __syncwarp();
+            if (++pslot == STAGES) pslot = 0;
           }
-          umma_commit(a_empty);
-          g0 += static_cast<uint32_t>(nj);
+          if (leader) umma_commit(a_empty);
+          __syncwarp();
         }
       }
     } else {

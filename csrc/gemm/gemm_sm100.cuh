@@ -255,7 +255,7 @@ __global__ void __launch_bounds__(kThreadsBase + 32 * EW, 1) gemm_kernel(const _
   uint64_t* p_bar = tempty_bar + 2;          // [EW warps][kPBufs]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(p_bar + 8 * kPBufs);
 
-  const int warp = threadIdx.x >> 5;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);  // warp-uniform for the compiler, too
   const int lane = threadIdx.x & 31;
   const int Bt = p.b0 * p.b1;
   const bool dist = p.world > 1;
@@ -372,7 +372,12 @@ __global__ void __launch_bounds__(kThreadsBase + 32 * EW, 1) gemm_kernel(const _
     }
   } else if (warp == 1) {
     // ======================================================= MMA issuer
-    if (lane == 0) {
+    // The whole warp walks the tile loop (waits included) and one elected lane issues: warp-uniform operands keep
+    // the MMA descriptors in uniform registers.  Issued from inside `if (lane == 0)` every tcgen05.mma came out
+    // wrapped in an elect / R2UR / branch loop of ~14 dependent instructions (~100 clk per MMA: hidden behind
+    // N = 256 MMAs, but not behind the N = 64 / 128 ones of narrow problems).
+    {
+      const bool leader = elect_one();
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
@@ -393,16 +398,19 @@ __global__ void __launch_bounds__(kThreadsBase + 32 * EW, 1) gemm_kernel(const _
           tc_fence_after();
           const uint32_t sa = smem_u32(smem_ab + stage * kStageBytes);
           const uint32_t sb = sa + kStageABytes;
+          if (leader) {
 #pragma unroll
-          for (int kk = 0; kk < BK / UK; ++kk) {
-            const uint64_t adesc = A_MN ? umma_smem_desc(sa + kk * UK * 128, mn_lbo, mn_sbo, kMnType)
-                                        : umma_smem_desc(sa + kk * 32, 16, 1024);
-            const uint64_t bdesc = B_MN ? umma_smem_desc(sb + kk * UK * 128, mn_lbo, mn_sbo, kMnType)
-                                        : umma_smem_desc(sb + kk * 32, 16, 1024);
-            umma_ss<DT == DDP_F32>(d_tmem, adesc, bdesc, kIdesc, (it | kk) != 0 ? 1u : 0u);
+            for (int kk = 0; kk < BK / UK; ++kk) {
+              const uint64_t adesc = A_MN ? umma_smem_desc(sa + kk * UK * 128, mn_lbo, mn_sbo, kMnType)
+                                          : umma_smem_desc(sa + kk * 32, 16, 1024);
+              const uint64_t bdesc = B_MN ? umma_smem_desc(sb + kk * UK * 128, mn_lbo, mn_sbo, kMnType)
+                                          : umma_smem_desc(sb + kk * 32, 16, 1024);
+              umma_ss<DT == DDP_F32>(d_tmem, adesc, bdesc, kIdesc, (it | kk) != 0 ? 1u : 0u);
+            }
+            umma_commit(&empty_bar[stage]);
+            if (it == k_iters - 1) umma_commit(&tfull_bar[acc]);
           }
-          umma_commit(&empty_bar[stage]);
-          if (it == k_iters - 1) umma_commit(&tfull_bar[acc]);
+          __syncwarp();
           if (++stage == STAGES) {
             stage = 0;
             phase ^= 1;
