@@ -40,7 +40,14 @@ def parse():
     ap.add_argument('--heads', type=int, default=HEADS)
     ap.add_argument('--d-model', type=int, default=D_MODEL)
     ap.add_argument('--offset', type=int, default=1024)
-    ap.add_argument('--dtype', type=str, default='bf16')
+    ap.add_argument('--dtype', type=str, default='bf16', help='ours: bf16 | fp16 | fp32 (fp32 storage, TF32 math)')
+    ap.add_argument('--ref-autocast', type=str, default='none', choices=['none', 'bf16'],
+                    help='reference arm: run the stock module inside torch.autocast(cuda, bfloat16)')
+    ap.add_argument('--mask', type=str, default='zeros', choices=['none', 'zeros', 'causal', 'random'],
+                    help="attention mask: the reference example's all-False mask (default), none, causal, or 30%% random")
+    ap.add_argument('--mask-refresh', type=int, default=0,
+                    help='build a NEW mask tensor every this many steps (0 = one mask for the whole run), so that '
+                         'the packed-mask cache of the slab-free path misses and the byte mask is read again')
     return ap.parse_args()
 
 
@@ -168,13 +175,36 @@ def main():
     y_host = torch.rand(1, tn, args.d_model).to(dtype).pin_memory()
     x_dev = x_host.to(dev)
     y_dev = y_host.to(dev)
-    mask = torch.zeros(1, tn, total_t, device=dev).bool()  # the reference example's all-False mask
+    def make_mask():
+        if args.mask == 'none':
+            return None
+        if args.mask == 'zeros':
+            return torch.zeros(1, tn, total_t, device=dev).bool()  # the reference example's all-False mask
+        if args.mask == 'causal':
+            rows = torch.arange(rank * tn, (rank + 1) * tn, device=dev).view(1, tn, 1)
+            return torch.arange(total_t, device=dev).view(1, 1, total_t) > rows
+        g = torch.Generator(device=dev)
+        g.manual_seed(333 + rank)
+        return torch.rand(1, tn, total_t, device=dev, generator=g) < 0.3
+
+    if reference and args.mask == 'none':
+        raise SystemExit('the reference module needs a bool mask (module.py:66)')
+    state = {'mask': make_mask(), 'n': 0}
     loss_host = torch.zeros(1, dtype=torch.float32).pin_memory()
+    autocast = reference and args.ref_autocast == 'bf16'
 
     def step(x, y):
+        if args.mask_refresh and state['n'] and state['n'] % args.mask_refresh == 0:
+            state['mask'] = make_mask()   # a new tensor object: nothing cached for the old one can be reused
+        state['n'] += 1
+        mask = state['mask']
         for p in model.parameters():
             p.grad = None
-        out = model(x, x, x, mask)
+        if autocast:
+            with torch.autocast('cuda', dtype=torch.bfloat16):
+                out = model(x, x, x, mask)
+        else:
+            out = model(x, x, x, mask)
         loss = torch.nn.functional.mse_loss(out.float(), y.float())
         loss.backward()
         return loss
@@ -203,6 +233,7 @@ def main():
 
     result = {'impl': args.impl}
     attention_path = None
+    self_check = None
     try:
         if not reference:
             # Self-check of the slab-free attention kernels against the slab path on this very configuration
@@ -211,20 +242,37 @@ def main():
             from distributed_dot_product.parallel.runtime import check_status
             attention_path = 'slab'
             if att.FLASH_TRAIN and dtype in (torch.bfloat16, torch.float16):
+                # element-wise: output and input gradient of the slab-free path against the slab path
+                def probe():
+                    xg = x_dev.clone().requires_grad_(True)
+                    for p in model.parameters():
+                        p.grad = None
+                    out = model(xg, xg, xg, state['mask'])
+                    torch.nn.functional.mse_loss(out.float(), y_dev.float()).backward()
+                    return out.detach().float(), xg.grad.float()
+
+                ok = 0.0
                 try:
-                    l_flash = float(step(x_dev, y_dev))
+                    o_f, g_f = probe()
                     check_status()
                     att.FLASH_TRAIN = False
-                    l_slab = float(step(x_dev, y_dev))
-                    ok = abs(l_flash - l_slab) <= 2e-2 * abs(l_slab) + 1e-6
-                    flag = torch.tensor([1.0 if ok else 0.0], device=dev)
-                    if world > 1:
-                        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
-                    att.FLASH_TRAIN = bool(flag.item() > 0)
+                    o_s, g_s = probe()
+                    e_out = ((o_f - o_s).abs().max() / o_s.abs().max().clamp_min(1e-12)).item()
+                    e_grad = ((g_f - g_s).abs().max() / g_s.abs().max().clamp_min(1e-30)).item()
+                    self_check = {'max_rel_err_out': e_out, 'max_rel_err_x_grad': e_grad, 'against': 'slab path'}
+                    ok = 1.0 if (e_out <= 3e-2 and e_grad <= 3e-2) else 0.0
+                    del o_f, g_f, o_s, g_s
                 except RuntimeError as e:  # watchdog / peer timeout: keep the proven path
                     sys.stderr.write('slab-free attention self-check failed: %s\n' % e)
-                    att.FLASH_TRAIN = False
+                    self_check = {'error': str(e).splitlines()[0][:200]}
+                flag = torch.tensor([ok], device=dev)
+                if world > 1:  # every rank gets here, also the one that raised
+                    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+                att.FLASH_TRAIN = bool(flag.item() > 0)
                 attention_path = 'slab-free (flash)' if att.FLASH_TRAIN else 'slab (self-check rejected slab-free path)'
+                torch.cuda.empty_cache()
+            elif dtype == torch.float32:
+                attention_path = 'slab (fp32 storage, TF32 tensor-core math)'
         torch.cuda.reset_peak_memory_stats()  # the self-check's slab step must not count as this path's peak
         for _ in range(max(args.warmup, 3)):
             step(x_dev, y_dev)
@@ -260,15 +308,23 @@ def main():
         h2d = x_host.numel() * x_host.element_size() + y_host.numel() * y_host.element_size()
         flops_fwd = 4.0 * 2 * tn * args.d_model * args.d_model + 2 * 2.0 * tn * total_t * args.d_model
         result.update({
-            'metric': 'DistributedDotProductAttn fwd+bwd ms/step (16 heads, d_model=1024, T/N=8192)',
+            'metric': ('DistributedDotProductAttn fwd+bwd ms/step (16 heads, d_model=1024, T/N=8192)' if not args.T
+                       else 'DistributedDotProductAttn fwd+bwd ms/step (%d heads, d_model=%d, T=%d)'
+                       % (args.heads, args.d_model, total_t)),
             'value': ms, 'unit': 'ms', 'n_gpus': world, 'steps': args.steps, 'warmup': max(args.warmup, 3),
-            'ms_per_step': ms, 'higher_is_better': False, 'scaling': 'weak', 'vs_baseline': None,
-            'dtype': 'fp32 storage, tf32 matmul (reference native dtype)' if reference else args.dtype,
+            'ms_per_step': ms, 'higher_is_better': False, 'scaling': 'strong' if args.T else 'weak',
+            'vs_baseline': None,
+            'work_normalised_ms': ms / world,  # per-GPU attention work grows with N at fixed rows per GPU
+            'dtype': (('bf16 autocast over fp32 weights (stock reference module under torch.autocast)' if autocast
+                       else 'fp32 storage, tf32 matmul (reference native dtype)') if reference
+                      else ('fp32 storage, tf32 matmul' if args.dtype == 'fp32' else args.dtype)),
             'data': 'synthetic',
             'config': {'model': 'DistributedDotProductAttn heads=%d d_model=%d' % (args.heads, args.d_model),
                        'global_batch': 1, 'seq_len': total_t, 'rows_per_gpu': tn,
                        'parallelism': 'sp%d (time axis split, all-gather-KV)' % world,
                        'offset': args.offset,
+                       'mask': args.mask + (' (new tensor every %d steps)' % args.mask_refresh
+                                            if args.mask_refresh else ' (one tensor for the run)'),
                        'l2': 'L2 flushed between timed steps (256 MB device write outside the per-step event pairs)',
                        'attention_path': attention_path if attention_path else 'reference (slab)',
                        'scaling_note': 'rows per GPU fixed; per-GPU attention FLOPs grow with N (T^2/N)'},
@@ -279,6 +335,8 @@ def main():
             'loss': float(loss_host.item()),
             'peak_mem_gb': torch.cuda.max_memory_allocated() / 1e9,
         })
+        if self_check is not None:
+            result['self_check'] = self_check
         if reference:
             result['gpu_launches_note'] = 'reference arm: library kernels only (cuBLAS/ATen/NCCL)'
     except torch.cuda.OutOfMemoryError as e:
