@@ -72,3 +72,11 @@ extern "C" int ddp_memset_async(void* ptr, int value, size_t bytes, void* stream
 extern "C" int ddp_read_u32(const void* dev_ptr, uint32_t* out) {
   return cuda_check(cudaMemcpy(out, dev_ptr, sizeof(uint32_t), cudaMemcpyDeviceToHost), "cudaMemcpy(status word)");
 }
+
+// Stream-ordered copy of a device word into PINNED host memory: the Python runtime polls the sticky status word
+// this way every few collective calls without ever synchronising the device (parallel/runtime.py).
+extern "C" int ddp_read_u32_async(const void* dev_ptr, uint32_t* pinned_host, void* stream) {
+  return cuda_check(cudaMemcpyAsync(pinned_host, dev_ptr, sizeof(uint32_t), cudaMemcpyDeviceToHost,
+                                    static_cast<cudaStream_t>(stream)),
+                    "cudaMemcpyAsync(status word)");
+}

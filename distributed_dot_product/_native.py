@@ -92,6 +92,7 @@ def load():
         lib.ddp_heap_open.argtypes = [c.c_void_p, c.POINTER(c.c_void_p)]
         lib.ddp_heap_close.argtypes = [c.c_void_p]
         lib.ddp_heap_free.argtypes = [c.c_void_p]
+        lib.ddp_read_u32_async.argtypes = [c.c_void_p, c.c_void_p, c.c_void_p]
         lib.ddp_attn_fwd_workspace.argtypes = [tp, tp, c.c_int, c.c_int, c.POINTER(c.c_size_t), c.POINTER(c.c_size_t)]
         lib.ddp_attn_fwd.argtypes = [tp, tp, tp, tp, c.c_void_p, c.c_void_p, c.c_int64, c.c_int64, c.c_float,
                                      c.POINTER(Comm), c.c_int, c.c_void_p]

@@ -135,6 +135,8 @@ class _Heap(object):
         self.seq = 0
         self.comm = [None, None]  # prebuilt ctypes structs per parity
         self.generation = 0
+        self._stream = None       # the one stream the collective kernels are enqueued on
+        self._status_host = None  # pinned mirror of the status word (see next_comm)
 
     @classmethod
     def get(cls):
@@ -156,6 +158,7 @@ class _Heap(object):
         self.base = None
         self.peers = []
         self.ws_cap = self.flag_cap = 0
+        self._stream = None
 
     def ensure(self, ws_bytes, n_flags):
         """Collective when it has to grow: every rank passes the same sizes in the same call."""
@@ -200,12 +203,42 @@ class _Heap(object):
             cm.status = self.base + 384
             self.comm[parity] = cm
 
+    #: poll the sticky status word every this many collective calls (stream-ordered copy, no device sync)
+    POLL_EVERY = 64
+
     def next_comm(self, chunk_rows):
+        """The communication block of the next collective call (sequence number = epoch of its flags).
+
+        The epoch / parity protocol assumes that every collective kernel of this process is enqueued on ONE
+        stream, in the same order on every rank; a second stream would let call ``seq`` overtake ``seq - 1`` and
+        reuse a workspace parity that is still being read.  The first call fixes the stream, later calls from
+        another stream raise.  Every ``POLL_EVERY`` calls the status word is copied to pinned host memory in
+        stream order and the value of the PREVIOUS poll is examined, so a peer that timed out turns into an
+        exception within at most 2 * POLL_EVERY calls without a single device synchronisation."""
+        stream = torch.cuda.current_stream().cuda_stream
+        if self._stream is None:
+            self._stream = stream
+        elif stream != self._stream:
+            raise RuntimeError('distributed-dot-product: collective kernels must be enqueued on one stream '
+                               '(first call used stream %#x, this one %#x)' % (self._stream, stream))
         self.seq += 1
+        if self.seq % self.POLL_EVERY == 0:
+            self._poll_status(stream)
         cm = self.comm[self.seq & 1]
         cm.seq = self.seq
         cm.chunk_rows = int(chunk_rows)
         return cm
+
+    def _poll_status(self, stream):
+        lib = _native.load()
+        if self._status_host is None:
+            self._status_host = torch.zeros(1, dtype=torch.int32).pin_memory()
+        elif int(self._status_host[0]) != 0:   # written by the copy enqueued POLL_EVERY calls ago
+            raise RuntimeError('distributed-dot-product: a fused kernel timed out waiting for a peer '
+                               '(wait id %d); results since then are invalid' % int(self._status_host[0]))
+        _native.check(lib.ddp_read_u32_async(ctypes.c_void_p(self.base + 384),
+                                             ctypes.c_void_p(self._status_host.data_ptr()),
+                                             ctypes.c_void_p(stream)))
 
 
 def heap():
@@ -227,8 +260,8 @@ def check_status():
     torch.cuda.synchronize()
     site = max(lib.ddp_debug_timeout_site(), lib.ddp_debug_timeout_site_rowops(), lib.ddp_debug_timeout_site_attn())
     if site > 0:
-        raise RuntimeError('distributed-dot-product: an in-kernel pipeline wait gave up after 4 s (site %d: '
-                           '1 smem slot, 2 TMEM buffer, 3 operands, 4 accumulator, 5 P chunk, 6 softmax row, 11-19 attention forward); results are '
+        raise RuntimeError('distributed-dot-product: an in-kernel pipeline (mbarrier) wait gave up after 4 s (site %d: '
+                           '1 smem slot, 2 TMEM buffer, 3 operands, 4 accumulator, 5 P chunk, 6 softmax row, 11-59 attention kernels); results are '
                            'invalid - please report this shape' % site)
     hp = _Heap._instance
     if hp is None or hp.base is None:

@@ -207,6 +207,9 @@ int ddp_heap_free(void* ptr);
 int ddp_memset_async(void* ptr, int value, size_t bytes, void* stream);
 /* Synchronous read of one device word (the sticky status word of ddp_comm). */
 int ddp_read_u32(const void* dev_ptr, uint32_t* out);
+/* Stream-ordered copy of one device word into pinned host memory (no device synchronisation): the runtime polls
+ * the status word with it every few collective calls. */
+int ddp_read_u32_async(const void* dev_ptr, uint32_t* pinned_host, void* stream);
 
 #ifdef __cplusplus
 }
