@@ -33,6 +33,7 @@ HEADERS = [
     "csrc/attn/attn_fwd_sm100.cuh",
     "csrc/attn/attn_bwd_sm100.cuh",
     "csrc/attn/attn_fwd2_sm100.cuh",
+    "csrc/attn/attn_bwd2_sm100.cuh",
 ]
 LIB_OUT = "distributed_dot_product/_lib/libddp_b200.so"
 # `python build.py trace`: separate objects + build/attn_harness_trace with the pipeline time stamps of the

@@ -10,6 +10,7 @@
 #include "../gemm/tma_map.h"
 #include "attn_bwd_sm100.cuh"
 #include "attn_fwd2_sm100.cuh"
+#include "attn_bwd2_sm100.cuh"
 
 namespace ddp {
 
@@ -326,8 +327,18 @@ extern "C" int ddp_attn_bwd_rows(const ddp_tensor* A, const ddp_tensor* G, const
   } else {
     p.phase_mask = 3; p.chunk_rows = 1 << 30; p.n_chunks = 1;
   }
-  const long long items = (long long)p.b1 * p.m_pairs * p.b0;
   const int sms = ddp_num_sms();
+  if (!(p.dbg & 64)) {  // second generation: one 128-row block per item, dS stays in tensor memory
+    constexpr int kSmem2 = 3 * kAtTile + kAb2Stages * kAb2RowsStage + (2 * kAb2Stages + 8) * 8 + 16 + 1024;
+    static_assert(kSmem2 <= 232448, "shared memory budget exceeded");
+    const long long items2 = (long long)p.b1 * m_blocks * p.b0;
+    int grid2 = world > 1 ? sms : (int)(items2 < sms ? items2 : sms);
+    if (grid2 < 1) grid2 = 1;
+    static bool cfg2_bf[64] = {}, cfg2_h[64] = {};
+    return dt == DDP_BF16 ? attn_bwd_launch(attn_bwd2_rows_kernel<DDP_BF16>, cfg2_bf, kSmem2, p, grid2, stream)
+                          : attn_bwd_launch(attn_bwd2_rows_kernel<DDP_F16>, cfg2_h, kSmem2, p, grid2, stream);
+  }
+  const long long items = (long long)p.b1 * p.m_pairs * p.b0;
   int grid = world > 1 ? sms : (int)(items < sms ? items : sms);
   if (grid < 1) grid = 1;
   static bool cfg_bf[64] = {}, cfg_h[64] = {};
