@@ -329,7 +329,7 @@ extern "C" int ddp_attn_bwd_rows(const ddp_tensor* A, const ddp_tensor* G, const
   }
   const int sms = ddp_num_sms();
   if (!(p.dbg & 64)) {  // second generation: one 128-row block per item, dS stays in tensor memory
-    constexpr int kSmem2 = 3 * kAtTile + kAb2Stages * kAb2RowsStage + (2 * kAb2Stages + 8) * 8 + 16 + 1024;
+    constexpr int kSmem2 = 3 * kAtTile + kAb2Stages * kAb2RowsStage + (2 * kAb2Stages + 12) * 8 + 16 + 1024;
     static_assert(kSmem2 <= 232448, "shared memory budget exceeded");
     const long long items2 = (long long)p.b1 * m_blocks * p.b0;
     int grid2 = world > 1 ? sms : (int)(items2 < sms ? items2 : sms);

@@ -6,13 +6,15 @@
 //
 // Both kernels: one 128-row (128-column) block per work item instead of a pair - twice as many items, so the
 // last wave of the flagship shape is 99 % full instead of 87 % - and TWO streams that take the 64-wide steps of
-// the item in turn (stream = step parity).  Each stream owns its own S / dP accumulators; the 16-bit dS (P^T,
-// dS^T) tile is written back over them with tcgen05.st and enters the accumulating product as the TMEM A operand:
-//     [acc += dS_s(j) . X_j]  [S_s(j+2), dP_s(j+2)]      issued back to back, executed in order by the tensor pipe
-// so the elementwise warps of a stream wait for nothing but their own next tile, and that tile is computed while
-// the other stream's warps run their exponentials.  No staging tile in shared memory, no "previous product has
-// read the staging tile" wait, no "tile consumed" hand-shake.  One whole-warp MMA issuer with an elected lane
-// (uniform-register operands), mask words and row statistics through the shared-memory ring.
+// the item in turn (stream = step parity).  Each stream owns its own S / dP accumulators and its own 16-bit dS
+// (P^T, dS^T) tile IN TENSOR MEMORY (tcgen05.st), which enters the accumulating product as the TMEM A operand.
+// Per stream the issuer runs
+//     [S_s(j+2), dP_s(j+2)]   as soon as the stream's warps hold S_s(j), dP_s(j) in registers
+//     [acc += dS_s(j) . X_j]  as soon as they have written dS_s(j)
+// so the next tiles of a stream are computed while its warps are still busy with the current ones, and the other
+// stream's exponentials fill the rest.  No staging tile in shared memory and no shared-memory traffic for the
+// product operand.  One whole-warp MMA issuer with an elected lane (uniform-register operands), mask words
+// through the shared-memory ring.
 #pragma once
 #include "attn_bwd_sm100.cuh"
 
@@ -24,8 +26,8 @@ constexpr int kAb2RowsStage = 2 * kAbHalfTile + 1024;  // B_j | V_j (64 rows eac
 // ============================================================================================================
 // Row side.  Work item = (batch, 128-row block, head); A and dO stay in shared memory, (B_j, V_j) stream by in
 // 64-row steps; step j belongs to stream j & 1.
-//   TMEM: stream s: S [128 s, +64)  dP [128 s + 64, +64);  dA [256, 320)
-//         dS of the thread (row, 32-column half h): 16 columns at the start of its S columns (128 s + 32 h)
+//   TMEM: stream s: S [128 s, +64)  dP [128 s + 64, +64);  dA [256, 320);  dS_s [320 + 32 s, +32)
+//         dS of the thread (row, 32-column half h): the 16 columns at 320 + 32 s + 16 h
 //   warp 0 producer, warp 1 MMA issuer, warp 2 TMEM alloc + all-gather pusher, warp 3 idle,
 //   warps 4-19 elementwise: warp = (stream s, column half h, lane quadrant q), thread = one row x 32 columns
 // ============================================================================================================
@@ -47,8 +49,10 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd2_rows_kernel(const __g
   uint64_t* a_full = bars + 2 * STAGES;
   uint64_t* a_empty = a_full + 1;
   uint64_t* s_full = a_empty + 1;    // [2] S_s and dP_s landed in TMEM
-  uint64_t* p_full = s_full + 2;     // [2] dS_s written over S_s by all 8 warps of the stream
-  uint64_t* o_final = p_full + 2;    // [1] the last product of the work item into dA finished
+  uint64_t* s_empty = s_full + 2;    // [2] all 8 warps of the stream hold them in registers
+  uint64_t* p_full = s_empty + 2;    // [2] dS_s written by all 8 warps of the stream
+  uint64_t* o_done = p_full + 2;     // [2] dA += dS_s B_j finished (dS_s may be overwritten)
+  uint64_t* o_final = o_done + 2;    // [1] the last product of the work item into dA finished
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_final + 1);
 
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
@@ -81,7 +85,9 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd2_rows_kernel(const __g
     mbar_init(a_empty, 1);
     for (int s = 0; s < 2; ++s) {
       mbar_init(&s_full[s], 1);
+      mbar_init(&s_empty[s], 8);
       mbar_init(&p_full[s], 8);
+      mbar_init(&o_done[s], 1);
     }
     mbar_init(o_final, 1);
     fence_mbar_init();
@@ -104,18 +110,23 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd2_rows_kernel(const __g
     setmaxnreg_dec<kAtRegsLow>();
     if (warp == 0) {
       // ===================================================== TMA producer
+      // (whole warp walks the loop and waits; one elected lane issues the copies, so that their operands are
+      //  warp-uniform: issued from inside `if (lane == 0)` every TMA instruction is wrapped in an elect / R2UR loop,
+      //  and the four small mask copies per step alone cost 0.1 ms of this kernel)
+      const bool leader = elect_one();
       uint32_t g = 0;  // running step count: ring slot g % STAGES
       uint32_t a_ph = 0;
       for (int it = blockIdx.x; it < items; it += gridDim.x) {
         int b1i, b0i, m0;
         decode(it, b1i, b0i, m0);
         const int b = b1i * p.b0 + b0i;
-        if (lane == 0) {
-          mbar_wait(a_empty, a_ph ^ 1, 61);
+        mbar_wait(a_empty, a_ph ^ 1, 61);
+        if (leader) {
           mbar_arrive_expect_tx(a_full, 2 * kAtTile);
           tma_load_5d(sA, &p.tmA, a_full, 0, 0, m0, b0i, b1i);
           tma_load_5d(sG, &p.tmG, a_full, 0, 0, m0, b0i, b1i);
         }
+        __syncwarp();
         a_ph ^= 1;
         for (int si = 0; si < p.world; ++si) {
           const int seg = (p.rank + si) % p.world;
@@ -126,7 +137,7 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd2_rows_kernel(const __g
             need_fence = true;
           }
           for (int nb = 0; nb < p.n_steps; ++nb, ++g) {
-            if (lane == 0) {
+            {
               const uint32_t slot = g & (STAGES - 1);
               if (need_fence) fence_proxy_async();
               mbar_wait(&kv_empty[slot], ((g / STAGES) & 1) ^ 1, 62);
@@ -135,23 +146,26 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd2_rows_kernel(const __g
               // mask words of the step: per 32-row group the 2 column words x 32 rows are contiguous in the packed mask
               int mask_bytes = 0, mask_groups = 0;
               const long long w0 = (static_cast<long long>(seg) * p.Tn + n0) >> 5;
-              if (p.mask_bits != nullptr) {
+              if (p.mask_bits != nullptr && !(p.dbg & 256)) {
                 mask_bytes = static_cast<int>(min(2ll, p.mb_ld - w0)) * 128;
                 mask_groups = min(4, (p.M - m0 + 31) / 32);
               }
-              mbar_arrive_expect_tx(&kv_full[slot], 2 * kAbHalfTile + mask_bytes * mask_groups);
-              for (int gq = 0; gq < mask_groups; ++gq) {
-                const uint32_t* src =
-                    p.mask_bits + b1i * p.mb_sb1 + ((static_cast<long long>(m0 >> 5) + gq) * p.mb_ld + w0) * 32;
-                bulk_load_1d(smem_u32(sb + 2 * kAbHalfTile + gq * 256), src, mask_bytes, &kv_full[slot]);
+              if (leader) {
+                mbar_arrive_expect_tx(&kv_full[slot], 2 * kAbHalfTile + mask_bytes * mask_groups);
+                for (int gq = 0; gq < mask_groups; ++gq) {
+                  const uint32_t* src =
+                      p.mask_bits + b1i * p.mb_sb1 + ((static_cast<long long>(m0 >> 5) + gq) * p.mb_ld + w0) * 32;
+                  bulk_load_1d(smem_u32(sb + 2 * kAbHalfTile + gq * 256), src, mask_bytes, &kv_full[slot]);
+                }
+                if (remote) {
+                  tma_load_5d(sb, &p.tmBg, &kv_full[slot], 0, 0, n0, b, seg);
+                  tma_load_5d(sb + kAbHalfTile, &p.tmVg, &kv_full[slot], 0, 0, n0, b, seg);
+                } else {
+                  tma_load_5d(sb, &p.tmB, &kv_full[slot], 0, 0, n0, b0i, b1i);
+                  tma_load_5d(sb + kAbHalfTile, &p.tmV, &kv_full[slot], 0, 0, n0, b0i, b1i);
+                }
               }
-              if (remote) {
-                tma_load_5d(sb, &p.tmBg, &kv_full[slot], 0, 0, n0, b, seg);
-                tma_load_5d(sb + kAbHalfTile, &p.tmVg, &kv_full[slot], 0, 0, n0, b, seg);
-              } else {
-                tma_load_5d(sb, &p.tmB, &kv_full[slot], 0, 0, n0, b0i, b1i);
-                tma_load_5d(sb + kAbHalfTile, &p.tmV, &kv_full[slot], 0, 0, n0, b0i, b1i);
-              }
+              __syncwarp();
             }
             need_fence = false;
           }
@@ -184,6 +198,25 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd2_rows_kernel(const __g
         }
         __syncwarp();
       };
+      uint32_t se_ph0 = 0, se_ph1 = 0;
+      auto issue_da = [&](uint32_t g, int j, bool last) {  // dA += dS_s(j) B_j, s = j & 1
+        const int s = j & 1;
+        mbar_wait(&p_full[s], s ? pf_ph1 : pf_ph0, 65);
+        if (s) pf_ph1 ^= 1; else pf_ph0 ^= 1;
+        tc_fence_after();
+        // the two 16-column dS runs of the stream (column halves h = 0, 1) are K slices 0-1 / 2-3;
+        // B_j as [K = j][N = d], MN-major
+        const uint64_t db = umma_smem_desc(sKV_u + (g & (STAGES - 1)) * kAb2RowsStage, kAbHalfTile, 1024, 2);
+        const uint32_t tD = tmem_base + 320 + s * 32;
+        if (leader) {
+#pragma unroll
+          for (int kk = 0; kk < 4; ++kk) umma_ts(tA, tD + kk * 8, db + 128 * kk, kIdA, (j | kk) != 0 ? 1u : 0u);
+          umma_commit(&o_done[s]);
+          if (last) umma_commit(o_final);
+          umma_commit(&kv_empty[g & (STAGES - 1)]);
+        }
+        __syncwarp();
+      };
       for (int it = blockIdx.x; it < items; it += gridDim.x) {
         mbar_wait(a_full, a_ph, 64);
         a_ph ^= 1;
@@ -192,24 +225,13 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd2_rows_kernel(const __g
         if (nj > 1) issue_sp(g0 + 1, 1);
         for (int j = 0; j < nj; ++j) {
           const int s = j & 1;
-          const uint32_t g = g0 + j;
-          mbar_wait(&p_full[s], s ? pf_ph1 : pf_ph0, 65);
-          if (s) pf_ph1 ^= 1; else pf_ph0 ^= 1;
-          tc_fence_after();
-          // dA += dS_s B_j: the two 16-column dS runs of the stream (column halves h = 0, 1) are K slices 0-1 / 2-3;
-          // B_j as [K = j][N = d], MN-major
-          const uint64_t db = umma_smem_desc(sKV_u + (g & (STAGES - 1)) * kAb2RowsStage, kAbHalfTile, 1024, 2);
-          const uint32_t tS = tmem_base + s * 128;
-          if (leader) {
-#pragma unroll
-            for (int kk = 0; kk < 4; ++kk)
-              umma_ts(tA, tS + (kk >> 1) * 32 + (kk & 1) * 8, db + 128 * kk, kIdA, (j | kk) != 0 ? 1u : 0u);
-            if (j == nj - 1) umma_commit(o_final);
-            umma_commit(&kv_empty[g & (STAGES - 1)]);
-          }
-          __syncwarp();
-          if (j + 2 < nj) issue_sp(g + 2, s);
+          // the stream's warps hold S_s(j), dP_s(j): their accumulators are free for step j + 2
+          mbar_wait(&s_empty[s], s ? se_ph1 : se_ph0, 69);
+          if (s) se_ph1 ^= 1; else se_ph0 ^= 1;
+          if (j + 2 < nj) issue_sp(g0 + j + 2, s);
+          if (j > 0) issue_da(g0 + j - 1, j - 1, false);
         }
+        issue_da(g0 + nj - 1, nj - 1, true);
         if (leader) umma_commit(a_empty);
         __syncwarp();
         g0 += static_cast<uint32_t>(nj);
@@ -225,12 +247,13 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd2_rows_kernel(const __g
     const int h = (idx >> 2) & 1;  // 32-column half of the stream's 64-column steps
     const int s = idx >> 3;        // stream: steps j = s, s + 2, ...
     const uint32_t lane_base = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
-    const uint32_t tS = lane_base + s * 128 + h * 32;        // scores; dS goes over the first 16 columns
+    const uint32_t tS = lane_base + s * 128 + h * 32;        // scores
     const uint32_t tP = lane_base + s * 128 + 64 + h * 32;   // dP
-    const bool has_mask = p.mask_bits != nullptr;
+    const uint32_t tD = lane_base + 320 + s * 32 + h * 16;   // this thread's 16 columns of dS_s
+    const bool has_mask = p.mask_bits != nullptr && !(p.dbg & 512);
     const uint32_t mask_off = smem_u32(sKV) + 2 * kAbHalfTile + q * 256 + h * 128 + lane * 4;
     const uint32_t quad_bar = 1 + q;  // named barrier of the four warps of a lane quadrant (epilogue)
-    uint32_t sf_ph = 0, of_ph = 0;
+    uint32_t sf_ph = 0, of_ph = 0, od_ph = 0;
     uint32_t g0 = 0;  // running step count at the start of the item (ring slot of step j: (g0 + j) % STAGES)
     for (int it = blockIdx.x; it < items; it += gridDim.x) {
       int b1i, b0i, m0;
@@ -241,26 +264,30 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd2_rows_kernel(const __g
       const float neg_lse = p.neg_lse[static_cast<size_t>(b) * p.stat_ld + row_c];
       const float nds = p.nds[static_cast<size_t>(b) * p.stat_ld + row_c];
       int cur_nb = s % p.n_steps;  // 64-column block of step j inside its rank segment
+      bool sf_ok = false;
       for (int j = s; j < nj; j += 2) {
         const int nvalid = p.Tn - (cur_nb * kAbStep + h * 32);  // live columns of this thread's half (<= 0: none)
         cur_nb += 2;
         while (cur_nb >= p.n_steps) cur_nb -= p.n_steps;
-        uint32_t mk = 0u;
-        if (has_mask) {
-          const uint32_t g = g0 + j;
-          mbar_wait(&kv_full[g & (STAGES - 1)], (g / STAGES) & 1, 66);  // the mask words came with the step's tiles
-          mk = ld_shared_u32(mask_off + (g & (STAGES - 1)) * kAb2RowsStage);
-        }
-        if (nvalid < 32) mk = (nvalid <= 0) ? 0xffffffffu : (mk | (0xffffffffu << nvalid));
-        mbar_wait(&s_full[s], sf_ph, 67);
+        // Barrier waits cost ~100 clk of latency even when the phase is already complete, and the step is short:
+        // every wait is probed early (try_wait issued where its latency overlaps other work) and only blocks,
+        // at the point of use, if the probe failed.
+        if (!sf_ok) mbar_wait(&s_full[s], sf_ph, 67);
         sf_ph ^= 1;
         tc_fence_after();
         uint32_t rs[32], rp[32];
         tmem_ld_32x32(tS, rs);
         tmem_ld_32x32(tP, rp);
+        // the mask words came with the step's B / V tiles, which the score MMAs behind s_full have read: no wait
+        uint32_t mk = has_mask ? ld_shared_u32(mask_off + ((g0 + j) & (STAGES - 1)) * kAb2RowsStage) : 0u;
+        if (nvalid < 32) mk = (nvalid <= 0) ? 0xffffffffu : (mk | (0xffffffffu << nvalid));
+        const bool od_ok = mbar_try_wait(&o_done[s], od_ph ^ 1);
         tmem_ld_wait();
         tmem_ld_pin(rs);
         tmem_ld_pin(rp);
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&s_empty[s]);  // the accumulators may take the stream's next step
         // dS = exp2(scale_log2 S - L) * (scale dP - scale delta), packed 16-bit pairs
         uint32_t pk[16];
         if (mk == 0u) {
@@ -287,7 +314,13 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd2_rows_kernel(const __g
             pk[e / 2] = pack2<T>(v0, v1);
           }
         }
-        tmem_st_32x16(tS, pk);
+        // the stream's previous product has read dS_s (issued a whole stream period ago; passes at once on the
+        // stream's first step of the kernel)
+        if (!od_ok) mbar_wait(&o_done[s], od_ph ^ 1, 70);
+        od_ph ^= 1;
+        tc_fence_after();
+        tmem_st_32x16(tD, pk);
+        sf_ok = (j + 2 < nj) && mbar_try_wait(&s_full[s], sf_ph);  // probe of the stream's next tiles
         tmem_st_wait();
         tc_fence_before();
         __syncwarp();

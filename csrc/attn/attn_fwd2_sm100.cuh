@@ -112,6 +112,8 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_fwd2_kernel(const __grid_c
   setmaxnreg_dec<kAtRegsLow>();
   if (warp == 0) {
     // ======================================================= TMA producer (whole warp walks the loop)
+    // (one elected lane issues the copies with warp-uniform operands, see the MMA issuers below)
+    const bool leader = elect_one();
     int stage = 0;
     uint32_t ph = 0, a_ph = 0;
     const uint32_t* my_flags = p.flags[p.rank];
@@ -119,12 +121,13 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_fwd2_kernel(const __grid_c
       int b1i, b0i, m0;
       decode(it, b1i, b0i, m0);
       const int b = b1i * p.b0 + b0i;
-      if (lane == 0) {
-        mbar_wait(a_empty, a_ph ^ 1, 51);
+      mbar_wait(a_empty, a_ph ^ 1, 51);
+      if (leader) {
         mbar_arrive_expect_tx(a_full, 2 * kAtTile);
         tma_load_5d(sA, &p.tmA, a_full, 0, 0, m0, b0i, b1i);
         tma_load_5d(sA + kAtTile, &p.tmA, a_full, 0, 0, m0 + kAtBM, b0i, b1i);
       }
+      __syncwarp();
       a_ph ^= 1;
       for (int si = 0; si < p.world; ++si) {
         const int seg = (p.rank + si) % p.world;
@@ -142,7 +145,7 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_fwd2_kernel(const __grid_c
           need_fence = true;
         }
         for (int nb = 0; nb < p.n_blocks; ++nb) {
-          if (lane == 0) {
+          {
             if (need_fence) fence_proxy_async();  // peer (generic-proxy) writes -> our TMA (async-proxy) reads
             mbar_wait(&kv_empty[stage], ph ^ 1, 52);
             uint8_t* sb = sKV + stage * kAt2StageBytes;
@@ -157,19 +160,22 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_fwd2_kernel(const __grid_c
               mask_bytes = static_cast<int>(nw) * 128;
               mask_groups = min(8, (p.M - m0 + 31) / 32);
             }
-            mbar_arrive_expect_tx(&kv_full[stage], kAtStageBytes + mask_bytes * mask_groups);
-            for (int gq = 0; gq < mask_groups; ++gq) {
-              const uint32_t* src =
-                  p.mask_bits + b1i * p.mb_sb1 + ((static_cast<long long>(m0 >> 5) + gq) * p.mb_ld + w0) * 32;
-              bulk_load_1d(smem_u32(sb + kAtStageBytes + gq * 512), src, mask_bytes, &kv_full[stage]);
+            if (leader) {
+              mbar_arrive_expect_tx(&kv_full[stage], kAtStageBytes + mask_bytes * mask_groups);
+              for (int gq = 0; gq < mask_groups; ++gq) {
+                const uint32_t* src =
+                    p.mask_bits + b1i * p.mb_sb1 + ((static_cast<long long>(m0 >> 5) + gq) * p.mb_ld + w0) * 32;
+                bulk_load_1d(smem_u32(sb + kAtStageBytes + gq * 512), src, mask_bytes, &kv_full[stage]);
+              }
+              if (remote) {
+                tma_load_5d(sb, &p.tmBg, &kv_full[stage], 0, 0, n0, b, seg);
+                tma_load_5d(sb + kAtTile, &p.tmVg, &kv_full[stage], 0, 0, n0, b, seg);
+              } else {
+                tma_load_5d(sb, &p.tmB, &kv_full[stage], 0, 0, n0, b0i, b1i);
+                tma_load_5d(sb + kAtTile, &p.tmV, &kv_full[stage], 0, 0, n0, b0i, b1i);
+              }
             }
-            if (remote) {
-              tma_load_5d(sb, &p.tmBg, &kv_full[stage], 0, 0, n0, b, seg);
-              tma_load_5d(sb + kAtTile, &p.tmVg, &kv_full[stage], 0, 0, n0, b, seg);
-            } else {
-              tma_load_5d(sb, &p.tmB, &kv_full[stage], 0, 0, n0, b0i, b1i);
-              tma_load_5d(sb + kAtTile, &p.tmV, &kv_full[stage], 0, 0, n0, b0i, b1i);
-            }
+            __syncwarp();
           }
           need_fence = false;
           if (++stage == STAGES) {
@@ -333,7 +339,7 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_fwd2_kernel(const __grid_c
     const uint32_t mask_off = smem_u32(sKV) + kAtStageBytes + (w * 4 + q) * 512 + (h * 2) * 128 + lane * 4;
     uint32_t sf_ph = 0, of_ph = 0;
     uint32_t npv = 0;                // O_st += P V products issued for this stream so far (two per step)
-    uint32_t slot = 0, slot_ph = 0;  // ring position of the current step (for the mask tile)
+    uint32_t slot = 0;  // ring position of the current step (for the mask tile)
     for (int it = blockIdx.x; it < items; it += gridDim.x) {
       int b1i, b0i, m0;
       decode(it, b1i, b0i, m0);
@@ -348,13 +354,12 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_fwd2_kernel(const __grid_c
         const int nvalid = p.Tn - n0;            // live columns of the half (may be <= 0 or >= 64)
         uint32_t mk[2] = {0u, 0u};
         if (has_mask) {
-          mbar_wait(&kv_full[slot], slot_ph, 56);  // the mask tile landed with the step's B / V tiles
+          // the mask tile landed with the step's B / V tiles, which the score MMAs behind s_full have read; wait
+          // for the first sub-tile here (the wait in the sub-tile loop then passes at once)
+          mbar_wait(sf_bar, sf_ph, 56);
           mk[0] = ld_shared_u32(mask_off + slot * kAt2StageBytes);
           mk[1] = ld_shared_u32(mask_off + slot * kAt2StageBytes + 128);
-          if (++slot == STAGES) {
-            slot = 0;
-            slot_ph ^= 1;
-          }
+          if (++slot == STAGES) slot = 0;
         }
         if (nvalid < 64) {
 #pragma unroll
