@@ -369,7 +369,7 @@ static ColsLayout cols_layout(const ddp_tensor* B, const ddp_tensor* V, int worl
   L.p1_off = (L.p0_off + (size_t)world * Bt * V->rows * V->cols * 4 + al) & ~al;
   L.bytes = L.p1_off + (size_t)world * Bt * B->rows * B->cols * 4;
   L.gather_flags = 2 * (size_t)world * Bt * n_chunks;
-  L.flags = L.gather_flags + (size_t)world * Bt * n_mb * 8;
+  L.flags = L.gather_flags + (size_t)world * Bt * n_mb * 16;  // one per (source, batch, block, quadrant, part)
   return L;
 }
 
@@ -526,8 +526,18 @@ extern "C" int ddp_attn_bwd_cols(const ddp_tensor* A, const ddp_tensor* G, const
   } else {
     p.phase_mask = 7; p.chunk_rows = 1 << 30; p.n_chunks = 1;
   }
-  const long long items = (long long)world * p.b1 * p.m_pairs * p.b0;
   const int sms = ddp_num_sms();
+  if (!(p.dbg & 64)) {  // second generation: one 128-column block per item, P^T / dS^T stay in tensor memory
+    constexpr int kSmem2 = 4 * kAtTile + kAb2Stages * kAb2ColsStage + (2 * kAb2Stages + 12) * 8 + 16 + 1024;
+    static_assert(kSmem2 <= 232448, "shared memory budget exceeded");
+    const long long items2 = (long long)world * p.b1 * n_mb * p.b0;
+    int grid2 = world > 1 ? sms : (int)(items2 < sms ? items2 : sms);
+    if (grid2 < 1) grid2 = 1;
+    static bool cfg2_bf[64] = {}, cfg2_h[64] = {};
+    return dt == DDP_BF16 ? attn_bwd_launch(attn_bwd2_cols_kernel<DDP_BF16>, cfg2_bf, kSmem2, p, grid2, stream)
+                          : attn_bwd_launch(attn_bwd2_cols_kernel<DDP_F16>, cfg2_h, kSmem2, p, grid2, stream);
+  }
+  const long long items = (long long)world * p.b1 * p.m_pairs * p.b0;
   int grid = world > 1 ? sms : (int)(items < sms ? items : sms);
   if (grid < 1) grid = 1;
   static bool cfg_bf[64] = {}, cfg_h[64] = {};

@@ -405,6 +405,15 @@ __device__ __forceinline__ void ffma2(float& d0, float& d1, float a0, float a1, 
   asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(bb), "l"(cc));
   asm("mov.b64 {%0, %1}, %2;" : "=f"(d0), "=f"(d1) : "l"(d));
 }
+// (a0, a1) * b + (c0, c1)
+__device__ __forceinline__ void ffma2p(float& d0, float& d1, float a0, float a1, float b, float c0, float c1) {
+  uint64_t a, bb, cc, d;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(a) : "f"(a0), "f"(a1));
+  asm("mov.b64 %0, {%1, %1};" : "=l"(bb) : "f"(b));
+  asm("mov.b64 %0, {%1, %2};" : "=l"(cc) : "f"(c0), "f"(c1));
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(bb), "l"(cc));
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(d0), "=f"(d1) : "l"(d));
+}
 __device__ __forceinline__ void fadd2(float& d0, float& d1, float a0, float a1, float b0, float b1) {
   uint64_t a, b, d;
   asm("mov.b64 %0, {%1, %2};" : "=l"(a) : "f"(a0), "f"(a1));
