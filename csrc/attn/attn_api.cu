@@ -435,6 +435,64 @@ __global__ void pack_mask_il_kernel(const uint8_t* __restrict__ mask, long long 
 
 }  // namespace ddp
 
+// Row statistics of the slab-free backward in one launch: delta = rowsum(dO * O) per (row, head), then
+//   neg_lse[b][h][r] = -L            nds[b][h][r] = -scale * delta          (non-finite values -> 0: fully masked rows)
+// for r < rows and 0 for the padding rows r in [rows, stat_ld) - the two arrays the backward kernels stream.
+namespace ddp {
+template <typename T>
+__global__ void attn_bwd_stats_kernel(const T* __restrict__ g, const T* __restrict__ o, const float* __restrict__ lse,
+                                      float* __restrict__ neg_lse, float* __restrict__ nds, long long rows, int cols,
+                                      long long g_ld, long long g_sb0, long long g_sb1, long long o_ld, long long o_sb0,
+                                      long long o_sb1, int b0, long long n_bh, long long stat_ld, float scale) {
+  const long long wid = static_cast<long long>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (wid >= n_bh * stat_ld) return;
+  const int lane = threadIdx.x & 31;
+  const long long bh = wid / stat_ld, r = wid - bh * stat_ld;
+  float nl = 0.f, nd = 0.f;
+  if (r < rows) {
+    const long long b1i = bh / b0, b0i = bh - b1i * b0;
+    const T* gp = g + b1i * g_sb1 + b0i * g_sb0 + r * g_ld;
+    const T* op = o + b1i * o_sb1 + b0i * o_sb0 + r * o_ld;
+    float acc = 0.f;
+    for (int c = lane; c < cols; c += 32) acc += static_cast<float>(gp[c]) * static_cast<float>(op[c]);
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
+    nd = -scale * acc;
+    nl = -lse[bh * rows + r];
+    if (!(fabsf(nd) <= 3.0e38f)) nd = 0.f;  // NaN / inf
+    if (!(fabsf(nl) <= 3.0e38f)) nl = 0.f;
+  }
+  if (lane == 0) {
+    neg_lse[wid] = nl;
+    nds[wid] = nd;
+  }
+}
+}  // namespace ddp
+
+extern "C" int ddp_attn_bwd_stats(const ddp_tensor* G, const ddp_tensor* O, const float* lse, float* neg_lse, float* nds,
+                                  int64_t stat_ld, float scale, void* stream_) {
+  if (!G || !O || !lse || !neg_lse || !nds) return set_error(-4, "attn bwd stats: null argument");
+  if (G->dtype != O->dtype || G->rows != O->rows || G->cols != O->cols || G->b0 != O->b0 || G->b1 != O->b1)
+    return set_error(-4, "attn bwd stats: dO and O differ in shape or dtype");
+  if (stat_ld < G->rows) return set_error(-4, "attn bwd stats: stat_ld < rows");
+  const long long n_bh = (long long)G->b0 * G->b1;
+  const long long warps = n_bh * stat_ld;
+  const int wpb = 8;
+  const unsigned grid = (unsigned)((warps + wpb - 1) / wpb);
+  cudaStream_t st = static_cast<cudaStream_t>(stream_);
+  if (G->dtype == DDP_BF16)
+    ddp::attn_bwd_stats_kernel<__nv_bfloat16><<<grid, wpb * 32, 0, st>>>(
+        (const __nv_bfloat16*)G->ptr, (const __nv_bfloat16*)O->ptr, lse, neg_lse, nds, G->rows, (int)G->cols, G->ld, G->sb0,
+        G->sb1, O->ld, O->sb0, O->sb1, (int)G->b0, n_bh, stat_ld, scale);
+  else if (G->dtype == DDP_F16)
+    ddp::attn_bwd_stats_kernel<__half><<<grid, wpb * 32, 0, st>>>((const __half*)G->ptr, (const __half*)O->ptr, lse, neg_lse,
+                                                                  nds, G->rows, (int)G->cols, G->ld, G->sb0, G->sb1, O->ld,
+                                                                  O->sb0, O->sb1, (int)G->b0, n_bh, stat_ld, scale);
+  else
+    return set_error(-4, "attn bwd stats: 16-bit tensors only");
+  return ddp::cuda_check(cudaGetLastError(), "attn_bwd_stats launch");
+}
+
 extern "C" size_t ddp_attn_mask_words(int64_t b1, int64_t rows, int64_t cols, int transposed) {
   const int64_t own = transposed ? cols : rows, other = transposed ? rows : cols;
   return (size_t)b1 * (size_t)((own + 31) / 32) * (size_t)((other + 31) / 32) * 32;

@@ -97,6 +97,7 @@ def load():
         lib.ddp_attn_fwd.argtypes = [tp, tp, tp, tp, c.c_void_p, c.c_void_p, c.c_int64, c.c_int64, c.c_float,
                                      c.POINTER(Comm), c.c_int, c.c_void_p]
         lib.ddp_debug_timeout_site_attn.restype = c.c_int
+        lib.ddp_attn_bwd_stats.argtypes = [tp, tp, c.c_void_p, c.c_void_p, c.c_void_p, c.c_int64, c.c_float, c.c_void_p]
         lib.ddp_attn_bwd_rows.argtypes = [tp, tp, tp, tp, tp, c.c_void_p, c.c_void_p, c.c_int64, c.c_void_p, c.c_int64,
                                           c.c_int64, c.c_float, c.POINTER(Comm), c.c_int, c.c_void_p]
         lib.ddp_attn_bwd_cols_workspace.argtypes = [tp, tp, c.c_int, c.c_int, c.POINTER(c.c_size_t),

@@ -327,15 +327,18 @@ class _FlashAttentionCore(torch.autograd.Function):
         h, scale, offset = ctx.num_heads, ctx.scale, ctx.offset
         if not grad_out.is_contiguous():
             grad_out = grad_out.contiguous()
+        import ctypes
         b, tn, hd = grad_out.shape
-        dv = hd // h
-        # delta_i = rowsum(dO_i * O_i) per (row, head); the kernels want -L and -scale*delta as [B, H, stat_ld]
-        delta = _rowdot(grad_out.view(b * tn * h, dv), out.view(b * tn * h, dv)).view(b, tn, h)
+        # delta_i = rowsum(dO_i * O_i) per (row, head); the kernels want -L and -scale*delta as [B, H, stat_ld],
+        # zero-padded to a multiple of 64 rows: one native launch (ddp_attn_bwd_stats)
         stat_ld = (tn + 63) // 64 * 64
-        neg_lse = torch.zeros(b, h, stat_ld, dtype=torch.float32, device=keys.device)
-        nds = torch.zeros(b, h, stat_ld, dtype=torch.float32, device=keys.device)
-        neg_lse[..., :tn] = torch.nan_to_num(-lse, nan=0.0, posinf=0.0, neginf=0.0)
-        nds[..., :tn] = torch.nan_to_num(delta.transpose(1, 2) * (-scale), nan=0.0, posinf=0.0, neginf=0.0)
+        stats = torch.empty(2, b, h, stat_ld, dtype=torch.float32, device=keys.device)
+        neg_lse, nds = stats[0], stats[1]
+        vg, vo = _g.as_view(_heads(grad_out, h)), _g.as_view(_heads(out, h))
+        _native.check(_native.load().ddp_attn_bwd_stats(
+            ctypes.byref(vg), ctypes.byref(vo), ctypes.c_void_p(lse.data_ptr()), ctypes.c_void_p(neg_lse.data_ptr()),
+            ctypes.c_void_p(nds.data_ptr()), stat_ld, float(scale), _g._stream()))
+        _native.count_launch()
         d_keys, d_queries, d_values = torch.empty_like(keys), torch.empty_like(queries), torch.empty_like(values)
         flash_attention_backward(_heads(keys, h), _heads(queries, h), _heads(values, h), _heads(grad_out, h),
                                  neg_lse, nds, mask, scale, offset, _heads(d_keys, h), _heads(d_queries, h),

@@ -153,6 +153,11 @@ size_t ddp_attn_mask_words(int64_t b1, int64_t rows, int64_t cols, int transpose
 int ddp_attn_pack_mask(const uint8_t* mask, int64_t b1, int64_t rows, int64_t cols, int64_t mask_ld, int64_t mask_sb1,
                        uint32_t* bits, int transposed, void* stream);
 int ddp_debug_timeout_site_attn(void); /* pipeline watchdog of the attention kernels (sites 11-49) */
+/* Row statistics for ddp_attn_bwd_rows / ddp_attn_bwd_cols in one launch (replaces the autograd of the reference's
+ * softmax, module.py:65-67): neg_lse[b][h][r] = -lse, nds[b][h][r] = -scale * rowsum(dO * O), fp32 [b1*b0][stat_ld],
+ * zero for r >= rows; non-finite values (fully masked rows) become 0.  dO / O: [b1][b0][rows][dv] views. */
+int ddp_attn_bwd_stats(const ddp_tensor* dO, const ddp_tensor* O, const float* lse, float* neg_lse, float* nds,
+                       int64_t stat_ld, float scale, void* stream);
 /* Pipeline trace of ddp_attn_fwd (a profiling aid; the reference has only the `measure` printout,
  * multiplication/functions.py:24-41): while `device_buf` is non-null, CTA 0 of every forward launch stores
  * clock64() stamps of the first `steps` column steps of its first work item as [actors][steps][events] int64
