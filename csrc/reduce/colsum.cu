@@ -113,6 +113,59 @@ extern "C" int ddp_colsum(const ddp_tensor* x, void* out, void* scratch, size_t 
 }
 
 // ---------------------------------------------------------------------------------------------------------
+// Sum of S partial products (split-K weight gradients, ops/linear.py): out[i] = sum_s part[s][i], fp32 accumulate,
+// 16-byte vectors.  n must be a multiple of 16 / sizeof(T) and the pointers 16-byte aligned.
+namespace ddp {
+template <typename T>
+__global__ void sum_partials_kernel(const T* __restrict__ part, T* __restrict__ out, int splits, long long n_vec,
+                                    long long stride_vec) {
+  constexpr int VE = 16 / sizeof(T);
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= n_vec) return;
+  float acc[VE];
+#pragma unroll
+  for (int e = 0; e < VE; ++e) acc[e] = 0.f;
+  const uint4* src = reinterpret_cast<const uint4*>(part) + i;
+  for (int s = 0; s < splits; ++s) {
+    const uint4 v = src[s * stride_vec];
+    const T* t = reinterpret_cast<const T*>(&v);
+#pragma unroll
+    for (int e = 0; e < VE; ++e) acc[e] += static_cast<float>(t[e]);
+  }
+  uint4 o;
+  T* t = reinterpret_cast<T*>(&o);
+#pragma unroll
+  for (int e = 0; e < VE; ++e) t[e] = static_cast<T>(acc[e]);
+  reinterpret_cast<uint4*>(out)[i] = o;
+}
+}  // namespace ddp
+
+extern "C" int ddp_sum_partials(const void* part, void* out, int dtype, int splits, int64_t n, void* stream) {
+  const int es = dtype == DDP_F32 ? 4 : 2;
+  const int ve = 16 / es;
+  if (splits < 1 || n < 1) return set_error(-4, "sum_partials: empty input");
+  if (n % ve || (reinterpret_cast<uintptr_t>(part) & 15) || (reinterpret_cast<uintptr_t>(out) & 15))
+    return set_error(-2, "sum_partials: length must be a multiple of 16 bytes and the pointers 16-byte aligned");
+  const long long n_vec = n / ve;
+  const unsigned grid = static_cast<unsigned>((n_vec + 255) / 256);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  switch (dtype) {
+    case DDP_F32:
+      sum_partials_kernel<float><<<grid, 256, 0, st>>>((const float*)part, (float*)out, splits, n_vec, n_vec);
+      break;
+    case DDP_BF16:
+      sum_partials_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((const __nv_bfloat16*)part, (__nv_bfloat16*)out, splits,
+                                                                n_vec, n_vec);
+      break;
+    case DDP_F16:
+      sum_partials_kernel<__half><<<grid, 256, 0, st>>>((const __half*)part, (__half*)out, splits, n_vec, n_vec);
+      break;
+    default: return set_error(-4, "sum_partials: unsupported dtype");
+  }
+  return cuda_check(cudaGetLastError(), "sum_partials launch");
+}
+
+// ---------------------------------------------------------------------------------------------------------
 // Allocation-free variant.
 //
 // ddp_colsum needs a scratch buffer from its caller, and the usual caller gets one from an allocator.  Some

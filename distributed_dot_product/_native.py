@@ -88,6 +88,7 @@ def load():
         lib.ddp_colsum_scratch_bytes.argtypes = [c.c_int64, c.c_int64]
         lib.ddp_colsum_scratch_bytes.restype = c.c_size_t
         lib.ddp_colsum.argtypes = [tp, c.c_void_p, c.c_void_p, c.c_size_t, c.c_void_p]
+        lib.ddp_sum_partials.argtypes = [c.c_void_p, c.c_void_p, c.c_int, c.c_int, c.c_int64, c.c_void_p]
         lib.ddp_heap_alloc.argtypes = [c.c_size_t, c.POINTER(c.c_void_p), c.c_void_p]
         lib.ddp_heap_open.argtypes = [c.c_void_p, c.POINTER(c.c_void_p)]
         lib.ddp_heap_close.argtypes = [c.c_void_p]

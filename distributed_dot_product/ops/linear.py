@@ -44,8 +44,15 @@ def _weight_grad(g2, x2):
         return _g.gemm(_native.OP_TN, g2, x2, distributed=False)
     part = _g.gemm(_native.OP_TN, g2.view(split, rows // split, n_out), x2.view(split, rows // split, n_in),
                    distributed=False)
-    # fp32 sum of the S partial products in one native launch (column sum of the [S, n_out * n_in] view)
-    return colsum(part.view(split, n_out * n_in)).view(n_out, n_in)
+    # fp32 sum of the S partial products in one native launch
+    n = n_out * n_in
+    if (n * part.element_size()) % 16:
+        return colsum(part.view(split, n)).view(n_out, n_in)
+    out = torch.empty(n_out, n_in, dtype=part.dtype, device=part.device)
+    _native.check(_native.load().ddp_sum_partials(ctypes.c_void_p(part.data_ptr()), ctypes.c_void_p(out.data_ptr()),
+                                                  _g._DT[part.dtype], split, n, _g._stream()))
+    _native.count_launch()
+    return out
 
 
 class _Linear(torch.autograd.Function):

@@ -187,6 +187,9 @@ int ddp_rowdot(const ddp_tensor* a, const ddp_tensor* b, float* out, void* strea
  * row-split first stage; it may be NULL, then one CTA per 32 columns walks all the rows. */
 size_t ddp_colsum_scratch_bytes(int64_t rows, int64_t cols);
 int ddp_colsum(const ddp_tensor* x, void* out, void* scratch, size_t scratch_bytes, void* stream);
+/* out[i] = sum over s < splits of part[s * n + i], fp32 accumulate: the split-K reduction of the weight gradients
+ * (the reference lets cuBLAS/autograd do it inside nn.Linear, module.py:43-45).  n * sizeof(dtype) % 16 == 0. */
+int ddp_sum_partials(const void* part, void* out, int dtype, int splits, int64_t n, void* stream);
 
 /* Column sum for callers that cannot allocate (no counterpart in the reference).
  * Same result as ddp_colsum, but the fp32 partial sums go to a 4 MiB array built into the library instead of
