@@ -19,6 +19,7 @@ FLAGS = ARCH + ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "--expt
                 "-Xptxas", "-v"]
 LIB_SOURCES = [
     "csrc/runtime/runtime.cu",
+    "csrc/runtime/vmm_heap.cu",
     "csrc/gemm/gemm_api.cu",
     "csrc/softmax/softmax.cu",
     "csrc/reduce/colsum.cu",
