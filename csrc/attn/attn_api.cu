@@ -199,6 +199,7 @@ extern "C" int ddp_attn_fwd(const ddp_tensor* A, const ddp_tensor* B, const ddp_
     p.n_chunks = (int)((B->rows + chunk_rows - 1) / chunk_rows);
     for (int i = 0; i < world; ++i) {
       p.ws[i] = static_cast<char*>(comm->ws[i]);
+    p.mc_ws = static_cast<char*>(comm->mc_ws);
       p.flags[i] = comm->flags[i];
       p.done[i] = comm->done[i];
     }
@@ -266,6 +267,7 @@ static int attn_bwd_comm(AttnBwdParams& p, const ddp_tensor* B, const ddp_tensor
   p.n_chunks = (int)((B->rows + chunk_rows - 1) / chunk_rows);
   for (int i = 0; i < world; ++i) {
     p.ws[i] = static_cast<char*>(comm->ws[i]);
+    p.mc_ws = static_cast<char*>(comm->mc_ws);
     p.flags[i] = comm->flags[i];
     p.done[i] = comm->done[i];
   }

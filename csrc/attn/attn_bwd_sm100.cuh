@@ -49,6 +49,7 @@ struct alignas(64) AttnBwdParams {
   int phase_mask;
   int chunk_rows, n_chunks;
   char* ws[DDP_MAX_WORLD];
+  char* mc_ws;  // multicast alias of the workspace (null: unicast pushes)
   uint32_t* flags[DDP_MAX_WORLD];
   uint32_t* done[DDP_MAX_WORLD];
   uint32_t* exit_counter;
@@ -104,6 +105,15 @@ __device__ __forceinline__ void attn_push_gather(const AttnBwdParams& p, int Bt,
         jj[u] = v - rr[u] * vpr;
         if (v < nvec) qv[u] = ld_nc_v4(src + static_cast<long long>(rr[u]) * ld + jj[u] * 16);
       }
+      if (p.mc_ws != nullptr) {
+        // one multicast store: the switch writes the vector into every rank's gather buffer
+        char* dst = p.mc_ws + dst_off;
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int v = v0 + u * 32 + lane;
+          if (v < nvec) multimem_st_v4(dst + static_cast<size_t>(rr[u]) * rb + jj[u] * 16, qv[u]);
+        }
+      } else
       for (int i = 1; i < p.world; ++i) {
         const int peer = (p.rank - i + p.world) % p.world;
         char* dst = p.ws[peer] + dst_off;

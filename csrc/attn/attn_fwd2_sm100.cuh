@@ -298,6 +298,15 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_fwd2_kernel(const __grid_c
             jj[u] = v - rr[u] * vpr;
             if (v < nvec) qv[u] = ld_nc_v4(src + static_cast<long long>(rr[u]) * ld + jj[u] * 16);
           }
+          if (p.mc_ws != nullptr) {
+            // one multicast store: the switch writes the vector into every rank's gather buffer
+            char* dst = p.mc_ws + dst_off;
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const int v = v0 + u * 32 + lane;
+              if (v < nvec) multimem_st_v4(dst + static_cast<size_t>(rr[u]) * rb + jj[u] * 16, qv[u]);
+            }
+          } else
           for (int i = 1; i < p.world; ++i) {
             const int peer = (p.rank - i + p.world) % p.world;  // rank-1 consumes our rows first
             char* dst = p.ws[peer] + dst_off;

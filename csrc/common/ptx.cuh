@@ -334,6 +334,14 @@ __device__ __forceinline__ uint32_t ld_shared_u32(uint32_t saddr) {
 }
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
+// Store through an NVSwitch multicast address: the switch replicates the 16 bytes into every GPU bound to the
+// multicast object (the all-gather pushers: each byte leaves this GPU once instead of once per peer).
+__device__ __forceinline__ void multimem_st_v4(void* mc_ptr, const uint4& v) {
+  asm volatile("multimem.st.weak.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc_ptr), "r"(v.x), "r"(v.y), "r"(v.z),
+               "r"(v.w)
+               : "memory");
+}
+
 // ---------------------------------------------------------------- cross-GPU flags (system scope)
 __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
   uint32_t v;

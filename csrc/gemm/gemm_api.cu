@@ -369,6 +369,7 @@ extern "C" int ddp_gemm_ex(int op, const ddp_tensor* A, const ddp_tensor* B, con
     p.chunk_rows = chunk_rows; p.n_chunks = s.n_chunks;
     for (int i = 0; i < world; ++i) {
       p.ws[i] = static_cast<char*>(comm->ws[i]);
+      p.mc_ws = static_cast<char*>(comm->mc_ws);
       p.flags[i] = comm->flags[i];
       p.done[i] = comm->done[i];
     }

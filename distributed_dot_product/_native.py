@@ -30,7 +30,7 @@ class Comm(ctypes.Structure):
                 ('phase_mask', ctypes.c_int32), ('chunk_rows', ctypes.c_int32), ('_pad', ctypes.c_int32),
                 ('ws', ctypes.c_void_p * MAX_WORLD), ('flags', ctypes.c_void_p * MAX_WORLD),
                 ('done', ctypes.c_void_p * MAX_WORLD), ('exit_counter', ctypes.c_void_p),
-                ('status', ctypes.c_void_p)]
+                ('status', ctypes.c_void_p), ('mc_ws', ctypes.c_void_p)]
 
 
 class Epilogue(ctypes.Structure):
@@ -94,6 +94,14 @@ def load():
         lib.ddp_heap_close.argtypes = [c.c_void_p]
         lib.ddp_heap_free.argtypes = [c.c_void_p]
         lib.ddp_read_u32_async.argtypes = [c.c_void_p, c.c_void_p, c.c_void_p]
+        lib.ddp_vmm_query.argtypes = [c.POINTER(c.c_int), c.POINTER(c.c_int), c.POINTER(c.c_size_t)]
+        lib.ddp_vmm_alloc.argtypes = [c.c_size_t, c.POINTER(c.c_void_p), c.POINTER(c.c_int)]
+        lib.ddp_vmm_open.argtypes = [c.c_int, c.c_size_t, c.POINTER(c.c_void_p)]
+        lib.ddp_vmm_release.argtypes = [c.c_void_p]
+        lib.ddp_mc_create.argtypes = [c.c_size_t, c.c_int, c.POINTER(c.c_ulonglong), c.POINTER(c.c_int)]
+        lib.ddp_mc_import.argtypes = [c.c_int, c.POINTER(c.c_ulonglong)]
+        lib.ddp_mc_add_device.argtypes = [c.c_ulonglong]
+        lib.ddp_mc_bind.argtypes = [c.c_ulonglong, c.c_void_p, c.c_size_t, c.POINTER(c.c_void_p)]
         lib.ddp_attn_fwd_workspace.argtypes = [tp, tp, c.c_int, c.c_int, c.POINTER(c.c_size_t), c.POINTER(c.c_size_t)]
         lib.ddp_attn_fwd.argtypes = [tp, tp, tp, tp, c.c_void_p, c.c_void_p, c.c_int64, c.c_int64, c.c_float,
                                      c.POINTER(Comm), c.c_int, c.c_void_p]
@@ -115,6 +123,10 @@ def load():
         lib.ddp_memset_async.argtypes = [c.c_void_p, c.c_int, c.c_size_t, c.c_void_p]
         _lib = lib
     return _lib
+
+
+def last_error():
+    return load().ddp_last_error().decode()
 
 
 def check(code):

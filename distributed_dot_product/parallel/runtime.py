@@ -135,6 +135,9 @@ class _Heap(object):
         self.seq = 0
         self.comm = [None, None]  # prebuilt ctypes structs per parity
         self.generation = 0
+        self.backend = 'ipc'      # 'vmm' (cuMemCreate + POSIX descriptors) or 'ipc' (cudaMalloc + CUDA IPC)
+        self.mc_base = None       # multicast alias of the whole heap (vmm back end, NVSwitch multicast)
+        self.heap_note = ''       # why a better back end was not used (driver error text)
         self._stream = None       # the one stream the collective kernels are enqueued on
         self._status_host = None  # pinned mirror of the status word (see next_comm)
 
@@ -151,10 +154,18 @@ class _Heap(object):
         torch.cuda.synchronize()
         if _state['world'] > 1 and dist.is_initialized():
             dist.barrier()
-        for r, p in enumerate(self.peers):
-            if r != _state['rank'] and p:
-                lib.ddp_heap_close(ctypes.c_void_p(p))
-        lib.ddp_heap_free(ctypes.c_void_p(self.base))
+        if self.backend == 'vmm':
+            if self.mc_base:
+                lib.ddp_vmm_release(ctypes.c_void_p(self.mc_base))
+            for r, p in enumerate(self.peers):
+                if p:
+                    lib.ddp_vmm_release(ctypes.c_void_p(p))   # own mapping included
+        else:
+            for r, p in enumerate(self.peers):
+                if r != _state['rank'] and p:
+                    lib.ddp_heap_close(ctypes.c_void_p(p))
+            lib.ddp_heap_free(ctypes.c_void_p(self.base))
+        self.mc_base = None
         self.base = None
         self.peers = []
         self.ws_cap = self.flag_cap = 0
@@ -171,21 +182,7 @@ class _Heap(object):
         self.release()
         parity_bytes = new_ws + _align(new_flags * 4, 256)
         total = self.HEADER + 2 * parity_bytes
-        ptr = ctypes.c_void_p()
-        handle = ctypes.create_string_buffer(64)
-        _native.check(lib.ddp_heap_alloc(total, ctypes.byref(ptr), handle))
-        self.base = ptr.value
-        handles = [None] * world
-        dist.all_gather_object(handles, bytes(handle.raw))
-        self.peers = []
-        for r in range(world):
-            if r == rank:
-                self.peers.append(self.base)
-            else:
-                p = ctypes.c_void_p()
-                buf = ctypes.create_string_buffer(handles[r], 64)
-                _native.check(lib.ddp_heap_open(buf, ctypes.byref(p)))
-                self.peers.append(p.value)
+        self._allocate(total)
         torch.cuda.synchronize()
         dist.barrier()
         self.ws_cap, self.flag_cap = new_ws, new_flags
@@ -201,10 +198,162 @@ class _Heap(object):
                 cm.done[r] = self.peers[r]
             cm.exit_counter = self.base + 256
             cm.status = self.base + 384
+            cm.mc_ws = (self.mc_base + off) if self.mc_base else None
             self.comm[parity] = cm
 
     #: poll the sticky status word every this many collective calls (stream-ordered copy, no device sync)
     POLL_EVERY = 64
+
+    # ------------------------------------------------------------------ allocation back ends
+    def _allocate(self, total):
+        """Allocates this rank's heap and maps every peer's.  Back ends (``DDP_HEAP`` = auto | vmm | ipc):
+
+        * ``vmm``: CUDA virtual-memory-management allocations (``cuMemCreate``) exchanged as POSIX file descriptors
+          over unix-domain sockets, plus - where the driver and the fabric offer it and ``DDP_MULTICAST`` != 0 - one
+          multicast object over all ranks' heaps, whose address the all-gather pushers store to (``multimem.st``);
+        * ``ipc``: ``cudaMalloc`` + CUDA IPC handles (round-1 path), also the automatic fall-back.
+        The choice is collective: every rank reports whether its step worked and all ranks take the same branch."""
+        lib = _native.load()
+        world, rank = _state['world'], _state['rank']
+        want = os.environ.get('DDP_HEAP', 'auto')
+        self.backend, self.mc_base, self.heap_note = 'ipc', None, ''
+        if want in ('auto', 'vmm'):
+            fd_ok, mc_ok, gran = ctypes.c_int(0), ctypes.c_int(0), ctypes.c_size_t(0)
+            rc = lib.ddp_vmm_query(ctypes.byref(fd_ok), ctypes.byref(mc_ok), ctypes.byref(gran))
+            ok = rc == 0 and fd_ok.value != 0
+            note = '' if ok else ('ddp_vmm_query: %s' % (_native.last_error() if rc else 'no POSIX descriptor export'))
+            if self._all_ok(ok):
+                size = _align(total, gran.value)
+                ptr, fd = ctypes.c_void_p(), ctypes.c_int(-1)
+                rc = lib.ddp_vmm_alloc(size, ctypes.byref(ptr), ctypes.byref(fd))
+                if rc:
+                    note = _native.last_error()
+                if self._all_ok(rc == 0):
+                    fds = self._exchange_fds(fd.value)
+                    peers, good = [], True
+                    for r in range(world):
+                        if r == rank:
+                            peers.append(ptr.value)
+                            continue
+                        q = ctypes.c_void_p()
+                        if lib.ddp_vmm_open(fds[r], size, ctypes.byref(q)):
+                            good, note = False, _native.last_error()
+                            peers.append(None)
+                        else:
+                            peers.append(q.value)
+                    for r, f in enumerate(fds):
+                        if f is not None and f >= 0:
+                            os.close(f)
+                    if self._all_ok(good):
+                        self.backend, self.base, self.peers = 'vmm', ptr.value, peers
+                        self.vmm_size = size
+                        if mc_ok.value and world > 1 and os.environ.get('DDP_MULTICAST', '1') != '0':
+                            self._bind_multicast(size)
+                        return
+                    for q in peers:
+                        if q:
+                            lib.ddp_vmm_release(ctypes.c_void_p(q))
+                elif rc == 0:
+                    os.close(fd.value)
+                    lib.ddp_vmm_release(ptr)
+            self.heap_note = note
+            if want == 'vmm':
+                raise RuntimeError('DDP_HEAP=vmm: the VMM heap could not be set up on every rank (%s)' % note)
+        ptr = ctypes.c_void_p()
+        handle = ctypes.create_string_buffer(64)
+        _native.check(lib.ddp_heap_alloc(total, ctypes.byref(ptr), handle))
+        self.base = ptr.value
+        handles = [None] * world
+        dist.all_gather_object(handles, bytes(handle.raw))
+        self.peers = []
+        for r in range(world):
+            if r == rank:
+                self.peers.append(self.base)
+            else:
+                p = ctypes.c_void_p()
+                buf = ctypes.create_string_buffer(handles[r], 64)
+                _native.check(lib.ddp_heap_open(buf, ctypes.byref(p)))
+                self.peers.append(p.value)
+
+    @staticmethod
+    def _all_ok(ok):
+        """True iff ``ok`` holds on every rank (collective)."""
+        if _state['world'] == 1:
+            return bool(ok)
+        flags = [None] * _state['world']
+        dist.all_gather_object(flags, bool(ok))
+        return all(flags)
+
+    def _exchange_fds(self, fd):
+        """All-to-all of one file descriptor per rank (SCM_RIGHTS over abstract unix-domain sockets; the ranks of
+        a heap live on one node).  Returns the list of received descriptors, ``None`` at this rank's own index."""
+        import socket
+        import struct
+        world, rank = _state['world'], _state['rank']
+        fds = [None] * world
+        if world == 1:
+            os.close(fd)
+            return fds
+        self._fd_round = getattr(self, '_fd_round', 0) + 1
+        tag = '%s-%s-%d' % (os.environ.get('MASTER_PORT', '0'), os.environ.get('TORCHELASTIC_RUN_ID', 'x'),
+                            self._fd_round)
+        name = lambda r: '\0ddp-b200-heap-%s-%d' % (tag, r)
+        srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+        srv.bind(name(rank))
+        srv.listen(world)
+        dist.barrier()
+        for r in range(world):
+            if r == rank:
+                continue
+            c = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+            c.connect(name(r))
+            socket.send_fds(c, [struct.pack('i', rank)], [fd])
+            c.close()
+        for _ in range(world - 1):
+            conn, _addr = srv.accept()
+            msg, got, _flags, _a = socket.recv_fds(conn, 4, 1)
+            fds[struct.unpack('i', msg)[0]] = got[0]
+            conn.close()
+        srv.close()
+        os.close(fd)
+        dist.barrier()
+        return fds
+
+    def _bind_multicast(self, size):
+        """One multicast object over all ranks' heaps (collective; any failure leaves ``mc_base`` unset and the
+        pushers on unicast stores, with the driver's error in ``heap_note``)."""
+        lib = _native.load()
+        world, rank = _state['world'], _state['rank']
+        obj, fd = ctypes.c_ulonglong(0), ctypes.c_int(-1)
+        ok = True
+        if rank == 0:
+            ok = lib.ddp_mc_create(size, world, ctypes.byref(obj), ctypes.byref(fd)) == 0
+            if not ok:
+                self.heap_note = _native.last_error()
+        if not self._all_ok(ok):
+            self.heap_note = self.heap_note or 'rank 0 could not create the multicast object'
+            return
+        send = fd.value if rank == 0 else os.open(os.devnull, os.O_RDONLY)
+        fds = self._exchange_fds(send)
+        if rank != 0:
+            ok = lib.ddp_mc_import(fds[0], ctypes.byref(obj)) == 0
+        for f in fds:
+            if f is not None and f >= 0:
+                os.close(f)
+        if ok:
+            ok = lib.ddp_mc_add_device(obj.value) == 0
+        if not ok:
+            self.heap_note = _native.last_error()
+        if not self._all_ok(ok):      # also the barrier "every device added" that binding needs
+            return
+        mc = ctypes.c_void_p()
+        ok = lib.ddp_mc_bind(obj.value, ctypes.c_void_p(self.base), size, ctypes.byref(mc)) == 0
+        if not ok:
+            self.heap_note = _native.last_error()
+        if self._all_ok(ok):
+            self.mc_base = mc.value
+        elif ok:
+            lib.ddp_vmm_release(mc)
 
     def next_comm(self, chunk_rows):
         """The communication block of the next collective call (sequence number = epoch of its flags).

@@ -53,6 +53,8 @@ typedef struct ddp_comm {
   uint32_t* exit_counter;        /* one zero-initialised uint32 in local memory */
   uint32_t* status;              /* sticky error word in local memory (0 = ok); a wait on a peer that
                                     exceeds 20 s stores which wait (1..5) here instead of hanging; may be NULL */
+  void* mc_ws;                   /* NVSwitch multicast alias of the workspace (ddp_mc_bind): a store to mc_ws + off
+                                    lands at ws[r] + off of EVERY rank; NULL = push to each peer separately */
 } ddp_comm;
 
 const char* ddp_last_error(void);
@@ -208,6 +210,24 @@ int ddp_colsum_noalloc(const ddp_tensor* x, void* out, void* stream);
 
 /* ---- symmetric heap (runtime) ------------------------------------------------------------ */
 /* Allocates `bytes` of device memory suitable for peer mapping and returns a 64-byte IPC handle. */
+/* Symmetric heap on the virtual-memory-management driver API with an NVSwitch multicast alias (replaces the
+ * reference's Horovod / MPI transport, multiplication/functions.py:95,143,206; csrc/runtime/vmm_heap.cu):
+ *   ddp_vmm_query      what the device offers: POSIX descriptor export, multicast objects, allocation granularity
+ *   ddp_vmm_alloc      cuMemCreate + map + zero; *fd_out = descriptor to send to the peers (caller closes it)
+ *   ddp_vmm_open       map the allocation behind a descriptor received from a peer
+ *   ddp_vmm_release    unmap + drop the handle (own heap, peer mapping or multicast mapping)
+ *   ddp_mc_create / ddp_mc_import / ddp_mc_add_device / ddp_mc_bind
+ *                      one multicast object over every rank's heap; *mc_ptr + off addresses byte off of ALL heaps
+ * Every failure names the driver call and its CUresult in ddp_last_error(). */
+int ddp_vmm_query(int* fd_handles, int* multicast, size_t* granularity);
+int ddp_vmm_alloc(size_t bytes, void** ptr, int* fd_out);
+int ddp_vmm_open(int fd, size_t bytes, void** ptr);
+int ddp_vmm_release(void* ptr);
+int ddp_mc_create(size_t bytes, int n_devices, unsigned long long* object, int* fd_out);
+int ddp_mc_import(int fd, unsigned long long* object);
+int ddp_mc_add_device(unsigned long long object);
+int ddp_mc_bind(unsigned long long object, void* heap_ptr, size_t bytes, void** mc_ptr);
+/* cudaMalloc + CUDA IPC variant of the heap (fall-back when descriptors cannot be exported). */
 int ddp_heap_alloc(size_t bytes, void** ptr, void* ipc_handle_out64);
 int ddp_heap_open(const void* ipc_handle64, void** ptr);
 int ddp_heap_close(void* ptr);
