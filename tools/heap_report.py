@@ -22,7 +22,7 @@ import torch.distributed as dist
 parts = [torch.empty_like(a) for _ in range(world)]
 dist.all_gather(parts, a)
 ref = a.float() @ torch.cat(parts, 1).float().transpose(-1, -2)
-ok = bool((out.float() == ref).all())
+ok = bool((out.float() - ref).abs().max() <= 1e-2 * ref.abs().max())  # bf16 output: rounding only
 ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
 for _ in range(5):
     distributed_matmul_nt(a, a, offset=256)
@@ -31,7 +31,7 @@ ev[0].record()
 for _ in range(20):
     distributed_matmul_nt(a, a, offset=256)
 ev[1].record(); torch.cuda.synchronize()
-print('rank %d/%d: heap backend=%s multicast=%s note=%r exact=%s nt(T=%d,d=%d) %.3f ms'
+print('rank %d/%d: heap backend=%s multicast=%s note=%r correct=%s nt(T=%d,d=%d) %.3f ms'
       % (rank, world, hp.backend, bool(hp.mc_base), hp.heap_note, ok, t, d, ev[0].elapsed_time(ev[1]) / 20), flush=True)
 runtime.check_status()
 comm.shutdown()
