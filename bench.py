@@ -241,7 +241,13 @@ def main():
             import distributed_dot_product.ops.attention as att
             from distributed_dot_product.parallel.runtime import check_status
             attention_path = 'slab'
-            if att.FLASH_TRAIN and dtype in (torch.bfloat16, torch.float16):
+            # the slab path keeps P and dS ([heads, T/N, T] each) plus transients: only check against it when it fits
+            slab_bytes = 3.5 * args.heads * tn * total_t * 2
+            fits = slab_bytes < 0.8 * torch.cuda.mem_get_info()[0]
+            if att.FLASH_TRAIN and dtype in (torch.bfloat16, torch.float16) and not fits:
+                attention_path = 'slab-free (flash)'
+                self_check = {'skipped': 'the slab path needs ~%.0f GB at this shape' % (slab_bytes / 1e9)}
+            elif att.FLASH_TRAIN and dtype in (torch.bfloat16, torch.float16):
                 # element-wise: output and input gradient of the slab-free path against the slab path
                 def probe():
                     xg = x_dev.clone().requires_grad_(True)
@@ -342,6 +348,13 @@ def main():
     except torch.cuda.OutOfMemoryError as e:
         result = {'impl': args.impl, 'unavailable': 'CUDA out of memory at T=%d on %d GPU(s): %s'
                   % (total_t, world, str(e).split('.')[0])}
+    except RuntimeError as e:
+        if not (reference and autocast):
+            raise
+        # the stock reference cannot train under autocast: its hand-written backward runs outside the autocast
+        # region and multiplies an fp32 gradient with a bf16 operand (functions.py:96)
+        result = {'impl': args.impl, 'unavailable': 'stock reference under torch.autocast(bfloat16) raises in backward: %s'
+                  % str(e).splitlines()[0][:160]}
     if rank == 0:
         print(json.dumps(result))
     if world > 1:

@@ -6,7 +6,7 @@ mkdir -p $OUT
 RUN="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1"
 port=29800
 tr() { port=$((port+1)); timeout ${TMO:-400} $RUN --master-port $port "$@"; }
-b() { name=$1; shift; tr bench.py --gpus $N "$@" > $OUT/$name.log 2>&1; tail -1 $OUT/$name.log > $OUT/$name.json; cut -c1-220 $OUT/$name.json; }
+b() { name=$1; shift; tr bench.py --gpus $N "$@" > $OUT/$name.log 2>&1; grep -a '^{"impl"' $OUT/$name.log | tail -1 > $OUT/$name.json; cut -c1-220 $OUT/$name.json; }
 rm -f $OUT/sweep_ours.jsonl $OUT/sweep_reference.jsonl
 tr benchmarks/sweep.py --impl ours --out $OUT/sweep_ours.jsonl > $OUT/sweep_ours.log 2>&1; tail -2 $OUT/sweep_ours.log | cut -c1-200
 tr benchmarks/sweep.py --impl reference --iters 5 --out $OUT/sweep_reference.jsonl > $OUT/sweep_reference.log 2>&1; tail -2 $OUT/sweep_reference.log | cut -c1-200
