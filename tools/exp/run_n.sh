@@ -19,6 +19,9 @@ if [ "$MODE" = full ]; then
   b bench_ours_fp32 --steps 5 --warmup 3 --dtype fp32
   b bench_reference_autocast --impl reference --steps 3 --warmup 3 --ref-autocast bf16
   if [ $N -gt 1 ]; then
+    DDP_HEAP=ipc b bench_ours_heap_ipc --steps 10 --warmup 3
+    DDP_MULTICAST=0 b bench_ours_heap_vmm_unicast --steps 10 --warmup 3
+    DDP_HEAP=ipc tr tools/heap_report.py 2>&1 | grep -E "^rank 0" > $OUT/heap_report_ipc.log; cat $OUT/heap_report_ipc.log
     for m in 1 0; do DDP_MULTICAST=$m tr tools/heap_report.py 2>&1 | grep -E "^rank 0" ; done > $OUT/heap_report.log 2>&1; cat $OUT/heap_report.log
     python -m pytest tests/test_gpu_multirank.py -m gpu -q > $OUT/pytest_multirank.log 2>&1; tail -3 $OUT/pytest_multirank.log
   fi
