@@ -99,6 +99,14 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd2_rows_kernel(const __g
   const uint32_t tmem_base = *tmem_slot;
 
   auto decode = [&](int it, int& b1i, int& b0i, int& m0) {  // heads fastest: concurrent CTAs share mask rows in L2
+    if (p.dbg & 1024) {  // row blocks fastest: concurrent CTAs stream the SAME (B_j, V_j) tiles of one head
+      const int mb = it % m_blocks;
+      const int r = it / m_blocks;
+      b0i = r % p.b0;
+      b1i = r / p.b0;
+      m0 = mb * kAtBM;
+      return;
+    }
     b0i = it % p.b0;
     const int r = it / p.b0;
     const int mb = r % m_blocks;

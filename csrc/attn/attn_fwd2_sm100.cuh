@@ -101,6 +101,14 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_fwd2_kernel(const __grid_c
   // work item -> (outer batch, row-block pair, head); heads fastest so the CTAs that run at the same time share
   // their mask rows in L2
   auto decode = [&](int it, int& b1i, int& b0i, int& m0) {
+    if (p.dbg & 1024) {  // row-block pairs fastest: concurrent CTAs stream the SAME (B_j, V_j) tiles of one head
+      const int pair = it % p.m_pairs;
+      const int r = it / p.m_pairs;
+      b0i = r % p.b0;
+      b1i = r / p.b0;
+      m0 = pair * (2 * kAtBM);
+      return;
+    }
     b0i = it % p.b0;
     const int r = it / p.b0;
     const int pair = r % p.m_pairs;

@@ -708,6 +708,11 @@ int main(int argc, char** argv) {
     }
     return 0;
   }
+  if (mode == "perflong") {  // the per-GPU work of the 8-GPU flagship (8192 rows x 65536 columns) on one GPU
+    perf_case(DDP_BF16, 16, 8192, 65536, 64, true, 2);
+    perf_bwd(DDP_BF16, 16, 8192, 65536, 64, 2, true);
+    return 0;
+  }
   if (mode == "perfall") {  // timing only, all three kernels, with and without a (zero) bit mask
     perf_case(DDP_BF16, 16, 8192, 8192, 64, false, 5);
     perf_case(DDP_BF16, 16, 8192, 8192, 64, true, 5);

@@ -182,12 +182,13 @@ def _pack_mask(mask, b, h, tn, total, device, transposed=False):
     return bits, ldw, words // b
 
 
-def flash_attention_backward(k4, q4, v4, g4, neg_lse, nds, mask, scale, offset, dk4, dq4, dv4, bits=None):
+def flash_attention_backward(k4, q4, v4, g4, neg_lse, nds, mask, scale, offset, dk4, dq4, dv4, bits=None,
+                             which=3):
     """Backward of ``flash_attention_forward`` without any ``[T/N, T]`` slab: two deterministic kernels recompute
     the probability tiles from the forward's log-sum-exp (``neg_lse = -L``, ``nds = -scale * rowsum(dO * O)``,
     both fp32 ``[B, H, stat_ld]`` with ``stat_ld`` a multiple of 64).  ``dk4`` gets the row-side gradient
     (all-gather of q / v fused in), ``dq4`` / ``dv4`` the column-side ones (all-gather AND the reduce-scatter of
-    the ranks' partial sums fused in)."""
+    the ranks' partial sums fused in).  ``which``: bit 0 = row-side kernel, bit 1 = column-side kernel (tools)."""
     import ctypes
     from distributed_dot_product.parallel import runtime
     lib = _native.load()
@@ -217,16 +218,18 @@ def flash_attention_backward(k4, q4, v4, g4, neg_lse, nds, mask, scale, offset, 
         hp.ensure(ws.value, nf.value)
         return ctypes.byref(hp.next_comm(chunk))
 
-    _native.check(lib.ddp_attn_bwd_rows(
-        ctypes.byref(va), ctypes.byref(vg), ctypes.byref(vb), ctypes.byref(vv), ctypes.byref(vda), nl, nd, stat_ld,
-        ctypes.c_void_p(bits.data_ptr()) if bits is not None else None, ldw, sb1w, float(scale),
-        comm_for(lib.ddp_attn_fwd_workspace), 0, _g._stream()))
-    _native.count_launch()
-    _native.check(lib.ddp_attn_bwd_cols(
-        ctypes.byref(va), ctypes.byref(vg), ctypes.byref(vb), ctypes.byref(vv), ctypes.byref(vdv), ctypes.byref(vdb),
-        nl, nd, stat_ld, ctypes.c_void_p(bits_t.data_ptr()) if bits_t is not None else None, ldwt, sb1wt,
-        float(scale), comm_for(lib.ddp_attn_bwd_cols_workspace), 0, _g._stream()))
-    _native.count_launch()
+    if which & 1:
+        _native.check(lib.ddp_attn_bwd_rows(
+            ctypes.byref(va), ctypes.byref(vg), ctypes.byref(vb), ctypes.byref(vv), ctypes.byref(vda), nl, nd, stat_ld,
+            ctypes.c_void_p(bits.data_ptr()) if bits is not None else None, ldw, sb1w, float(scale),
+            comm_for(lib.ddp_attn_fwd_workspace), 0, _g._stream()))
+        _native.count_launch()
+    if which & 2:
+        _native.check(lib.ddp_attn_bwd_cols(
+            ctypes.byref(va), ctypes.byref(vg), ctypes.byref(vb), ctypes.byref(vv), ctypes.byref(vdv), ctypes.byref(vdb),
+            nl, nd, stat_ld, ctypes.c_void_p(bits_t.data_ptr()) if bits_t is not None else None, ldwt, sb1wt,
+            float(scale), comm_for(lib.ddp_attn_bwd_cols_workspace), 0, _g._stream()))
+        _native.count_launch()
 
 
 def _rowdot(a, b):
