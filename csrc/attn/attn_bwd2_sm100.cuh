@@ -481,12 +481,13 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd2_cols_kernel(const __g
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  // item -> (segment, outer batch, column block, head); segments rank-rotated with the own one LAST, so the partial
-  // sums for the other ranks leave early
+  // item -> (segment, outer batch, column block, head); segments rank-rotated with the own one FIRST: its B / V
+  // blocks are local, so the all-gather pushes of the peers (single pusher warps, ~0.2 ms for 2 x 16 MB) hide behind
+  // it.  (With the own segment last every CTA sat waiting for gathered rows at the start of the kernel.)
   auto decode = [&](int it, int& seg, int& b1i, int& b0i, int& c0) {
     const int si = it / per_seg;
     int r = it - si * per_seg;
-    seg = (p.rank + 1 + si) % p.world;
+    seg = (p.rank + si) % p.world;
     b0i = r % p.b0;
     r /= p.b0;
     const int mb = r % n_mb;
@@ -638,6 +639,7 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd2_cols_kernel(const __g
     uint32_t sf_ph = 0, of_ph = 0, od_ph = 0;
     uint32_t g0 = 0;
     uint32_t done_ok = 0;  // peers whose done counter this warp has already checked
+    uint32_t* pend_flag = nullptr;  // reduce-scatter flag of the previous work item, not yet published
     for (int it = blockIdx.x; it < items; it += gridDim.x) {
       int seg, b1i, b0i, c0;
       decode(it, seg, b1i, b0i, c0);
@@ -770,35 +772,65 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd2_cols_kernel(const __g
           __syncwarp();
           done_ok |= 1u << seg;
         }
+        if (pend_flag != nullptr) {  // the previous block's copies have had a whole work item to complete
+          bulk_wait_group<0>();
+          fence_proxy_async();
+          __threadfence_system();
+          st_release_sys(pend_flag, p.seq);
+          pend_flag = nullptr;
+        }
+        __syncwarp();
+        // The 32 columns of a lane quadrant are 32 consecutive rows of the owner's [Tn][cols] fp32 slot, i.e. ONE
+        // contiguous block: the four warps of the quadrant stage their 16-column parts in shared memory and one
+        // bulk copy (TMA engine, shared -> peer memory) moves the block.  (Per-thread 16-byte stores, lanes a row
+        // apart, crossed NVLink as 16-byte packets and cost ~0.4 ms per remote segment at the flagship shape.)
+        const uint32_t sbufq = smem_u32(sOut) + q * 8192;
 #pragma unroll
         for (int kind = 0; kind < 2; ++kind) {
           const int ncols = kind ? p.d : p.dv;
+          const uint32_t row_bytes = static_cast<uint32_t>(ncols) * 4u;
           uint32_t ra[16];
           tmem_ld_32x16(lane_base + 256 + kind * 64 + part * 16, ra);
           tmem_ld_wait();
           tmem_ld_pin16(ra);
-          if (col < p.Tn) {
-            float* dst = reinterpret_cast<float*>(p.ws[seg] + (kind ? p.ws_p1_off : p.ws_p0_off)) +
-                         ((static_cast<size_t>(p.rank) * Bt + b) * p.Tn + col) * ncols + part * 16;
 #pragma unroll
-            for (int c = 0; c < 4; ++c)
-              if (part * 16 + c * 4 < ncols) st_v4(dst + c * 4, make_uint4(ra[4 * c], ra[4 * c + 1], ra[4 * c + 2], ra[4 * c + 3]));
+          for (int c = 0; c < 4; ++c)
+            if (part * 16 + c * 4 < ncols)
+              st_shared_v4(sbufq + lane * row_bytes + part * 64 + c * 16,
+                           make_uint4(ra[4 * c], ra[4 * c + 1], ra[4 * c + 2], ra[4 * c + 3]));
+          tc_fence_before();
+          fence_proxy_async_smem();
+          named_bar_sync(quad_bar, 128);  // the block is staged (and all four warps have read this accumulator)
+          if (part == 0 && rows_valid > 0) {
+            if (lane == 0) {
+              char* dst = p.ws[seg] + (kind ? p.ws_p1_off : p.ws_p0_off) +
+                          ((static_cast<size_t>(p.rank) * Bt + b) * p.Tn + col0) * static_cast<size_t>(row_bytes);
+              bulk_store_1d(dst, sbufq, static_cast<uint32_t>(rows_valid) * row_bytes);
+              bulk_commit_group();
+              bulk_wait_group_read<0>();  // the staging block has been read; the writes are still in flight
+            }
+            __syncwarp();
           }
+          named_bar_sync(quad_bar, 128);  // the staging block may be overwritten
         }
-        tc_fence_before();
-        __threadfence_system();
-        __syncwarp();
-        if (lane == 0) {
+        // The flag of this block is published one work item later (or after the last one), once its bulk copies
+        // have completed: waiting for a copy across NVLink here would stall all 16 warps for its whole flight
+        // time (all CTAs push at the same moments, ~14 us per 64 KB block at the flagship shape).
+        if (part == 0 && lane == 0) {
           const size_t fidx = static_cast<size_t>(p.rs_flag_off) +
-                              (((static_cast<size_t>(p.rank) * Bt + b) * n_mb + c0 / kAtBM) * 4 + q) * 4 + part;
-          st_release_sys(p.flags[seg] + fidx, p.seq);
+                              (((static_cast<size_t>(p.rank) * Bt + b) * n_mb + c0 / kAtBM) * 4 + q) * 4;
+          pend_flag = p.flags[seg] + fidx;  // one flag per (source, batch, block, quadrant)
         }
-        __syncwarp();
-        // all four warps of the quadrant have read dV / dB before any of them starts the next item (whose first
-        // products overwrite the accumulators once BOTH streams' first dS tiles... of stream 0 are staged)
-        named_bar_sync(quad_bar, 128);
       }
     }
+    if (pend_flag != nullptr) {  // (lane 0 of the part-0 warps only)
+      bulk_wait_group<0>();
+      fence_proxy_async();
+      __threadfence_system();
+      st_release_sys(pend_flag, p.seq);
+      pend_flag = nullptr;
+    }
+    __syncwarp();
     // ---------------------------------------------------- reduce-scatter: owner-side reduction
     if (dist && do_reduce) {
       const int r_items = Bt * n_mb * 16;
@@ -809,35 +841,47 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd2_cols_kernel(const __g
         const int mb = r % n_mb;
         const int b = r / n_mb;
         if (lane < p.world) {
-          const size_t fidx = (((static_cast<size_t>(lane) * Bt + b) * n_mb + mb) * 4 + qq) * 4 + pt;
+          const size_t fidx = (((static_cast<size_t>(lane) * Bt + b) * n_mb + mb) * 4 + qq) * 4;
           wait_flag_ge(my_flags + fidx, p.seq, p.status, 5);
         }
         __syncwarp();
         const int b1i = b / p.b0, b0i = b - b1i * p.b0;
-        const int rrow = mb * kAtBM + qq * 32 + lane;
-        if (rrow < p.Tn) {
+        // 8 rows x all columns per warp item: 16 lanes read one row's 16-byte vectors (coalesced 256-byte rows),
+        // four rows per lane with the four loads of a source in flight together
+        const int vec = lane & 15, rsub = lane >> 4;
+        const int row0 = mb * kAtBM + qq * 32 + pt * 8 + rsub;
 #pragma unroll
-          for (int kind = 0; kind < 2; ++kind) {
-            const int ncols = kind ? p.d : p.dv;
-            const float* part_base = reinterpret_cast<const float*>(p.ws[p.rank] + (kind ? p.ws_p1_off : p.ws_p0_off));
-            const size_t src_stride = static_cast<size_t>(Bt) * p.Tn * ncols;
-            const float* src0 = part_base + (static_cast<size_t>(b) * p.Tn + rrow) * ncols + pt * 16;
-            T* out = reinterpret_cast<T*>(kind ? p.out1 : p.out0) + b1i * (kind ? p.o1_sb1 : p.o0_sb1) +
-                     b0i * (kind ? p.o1_sb0 : p.o0_sb0) + static_cast<long long>(rrow) * (kind ? p.ld1 : p.ld0) +
-                     pt * 16;
+        for (int kind = 0; kind < 2; ++kind) {
+          const int ncols = kind ? p.d : p.dv;
+          const bool vec_on = vec * 4 < ncols;
+          const float* part_base = reinterpret_cast<const float*>(p.ws[p.rank] + (kind ? p.ws_p1_off : p.ws_p0_off));
+          const size_t src_stride = static_cast<size_t>(Bt) * p.Tn * ncols;
+          const float* src0 = part_base + (static_cast<size_t>(b) * p.Tn + row0) * ncols + vec * 4;
+          float4 acc[4];
 #pragma unroll
-            for (int c = 0; c < 4; ++c) {
-              if (pt * 16 + c * 4 < ncols) {
-                float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-                for (int src = 0; src < p.world; ++src) {  // fixed order: deterministic
-                  const float4 t = *reinterpret_cast<const float4*>(src0 + src * src_stride + c * 4);
-                  acc.x += t.x; acc.y += t.y; acc.z += t.z; acc.w += t.w;
-                }
-                uint2 o;
-                o.x = pack2<T>(acc.x, acc.y);
-                o.y = pack2<T>(acc.z, acc.w);
-                *reinterpret_cast<uint2*>(out + c * 4) = o;
-              }
+          for (int i = 0; i < 4; ++i) acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+          for (int src = 0; src < p.world; ++src) {  // fixed order: deterministic
+            float4 t[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+              t[i] = (vec_on && row0 + 2 * i < p.Tn)
+                         ? *reinterpret_cast<const float4*>(src0 + src * src_stride + static_cast<size_t>(2 * i) * ncols)
+                         : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              acc[i].x += t[i].x; acc[i].y += t[i].y; acc[i].z += t[i].z; acc[i].w += t[i].w;
+            }
+          }
+          T* out = reinterpret_cast<T*>(kind ? p.out1 : p.out0) + b1i * (kind ? p.o1_sb1 : p.o0_sb1) +
+                   b0i * (kind ? p.o1_sb0 : p.o0_sb0) + vec * 4;
+          const long long ld = kind ? p.ld1 : p.ld0;
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            if (vec_on && row0 + 2 * i < p.Tn) {
+              uint2 o;
+              o.x = pack2<T>(acc[i].x, acc[i].y);
+              o.y = pack2<T>(acc[i].z, acc[i].w);
+              *reinterpret_cast<uint2*>(out + static_cast<long long>(row0 + 2 * i) * ld) = o;
             }
           }
         }

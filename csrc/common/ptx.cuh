@@ -133,6 +133,16 @@ __device__ __forceinline__ void tma_store_5d(const CUtensorMap* m, uint32_t smem
       ::"l"(reinterpret_cast<uint64_t>(m)), "r"(smem_src), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4)
       : "memory");
 }
+// 1-D bulk copy shared -> global (TMA engine, no tensor map; bulk async-group completion).  16-byte multiples.
+__device__ __forceinline__ void bulk_store_1d(void* gdst, uint32_t smem_src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_src), "r"(bytes)
+               : "memory");
+}
+// Wait until at most N of this thread's bulk groups are still in flight (writes performed, not only source read).
+template <int N>
+__device__ __forceinline__ void bulk_wait_group() {
+  asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory");
+}
 __device__ __forceinline__ void bulk_commit_group() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 // Wait until at most N of this thread's bulk groups still have to READ their shared-memory source.
 template <int N>
