@@ -122,6 +122,50 @@ def dump_sass():
             tc = {m: n for m, n in cnt.items() if any(m.startswith(p) for p in keys)}
             f.write("%s\n    %s\n" % (k, " ".join("%s=%d" % kv for kv in sorted(tc.items()))))
     print("wrote profiles/sass/mnemonics.txt (%d kernels)" % len(per_kernel))
+    # trimmed listings: every tcgen05 / TMA / mbarrier instruction of the hot kernels with its neighbourhood
+    want = {"attn_fwd2_kernelILi1ELi4ELb0": "attn_fwd2_bf16", "attn_bwd2_rows_kernelILi1": "attn_bwd2_rows_bf16",
+            "attn_bwd2_cols_kernelILi1": "attn_bwd2_cols_bf16", "gemm_kernelILi0ELi1ELi256ELi4ELi0ELi4": "gemm_nt_bf16_bn256",
+            "gemm_kernelILi1ELi1ELi256ELi4ELi0ELi4": "gemm_nn_bf16_bn256", "gemm_kernelILi2ELi1ELi128ELi6ELi0ELi4": "gemm_tn_bf16_bn128",
+            "gemm_kernelILi0ELi2ELi256": "gemm_nt_tf32_bn256"}
+    hot = re.compile(r"UTC|LDTM|STTM|UTMA|UBLKCP|SYNCS|MUFU|FFMA2|FADD2|FMUL2|ELECT|RED|ATOM|MEMBAR|FENCE")
+    cur, buf = None, []
+
+    def flush():
+        if not cur:
+            return
+        tag = next((v for k, v in want.items() if k in cur), None)
+        if tag is None or os.path.exists(os.path.join(out_dir, tag + ".sass.txt.done")):
+            return
+        keep = set()
+        for i, ln in enumerate(buf):
+            if hot.search(ln):
+                keep.update(range(max(0, i - 2), min(len(buf), i + 3)))
+        with open(os.path.join(out_dir, tag + ".sass.txt"), "w") as f:
+            f.write("# %s\n# cuobjdump -sass of %s, trimmed to the tcgen05 / TMA / mbarrier / MUFU instructions and two\n"
+                    "# neighbours each ('...' = omitted lines); %d of %d instructions shown\n" % (cur, LIB_OUT, len(keep), len(buf)))
+            last = -1
+            for i in sorted(keep):
+                if i != last + 1:
+                    f.write("        ...\n")
+                f.write(re.sub(r"\s*/\* 0x[0-9a-f]+ \*/\s*$", "", buf[i]) + "\n")
+                last = i
+        print("wrote profiles/sass/%s.sass.txt" % tag)
+
+    seen = set()
+    for line in sass.splitlines():
+        m = re.search(r"Function : (\S+)", line)
+        if m:
+            flush()
+            cur, buf = m.group(1), []
+            tag = next((v for k, v in want.items() if k in cur), None)
+            if tag in seen:
+                cur = None
+            elif tag:
+                seen.add(tag)
+            continue
+        if cur and re.match(r"^\s+/\*[0-9a-f]{4,}\*/", line):
+            buf.append(line.rstrip())
+    flush()
 
 
 if __name__ == "__main__":

@@ -147,6 +147,9 @@ def flash_attention_forward(k4, q4, v4, mask, scale, offset, out4, want_lse=Fals
 
 #: packed masks of the most recent calls, keyed by mask object identity (see _pack_mask)
 _MASK_CACHE = {}
+#: ``DDP_MASK_CACHE=0`` re-packs the mask on every call.  The cache trusts the tensor's version counter: writes that
+#: bypass it (``mask.data[...] = x``, a custom kernel, DLPack / numpy aliases) are not seen - disable the cache then.
+MASK_CACHE = bool(int(__import__('os').environ.get('DDP_MASK_CACHE', '1')))
 
 
 def _pack_mask(mask, b, h, tn, total, device, transposed=False):
@@ -163,8 +166,9 @@ def _pack_mask(mask, b, h, tn, total, device, transposed=False):
     # (storage, version counter, geometry) so that steady-state steps do not re-read the [T/N, T] byte mask.
     # Identity of the tensor OBJECT (weak reference) + its version counter: a new mask that merely lands on the
     # address of a freed one never matches.
-    key = (id(mask), t, b, tn, total)
-    hit = _MASK_CACHE.get(key)
+    # (the stream is part of the key: words packed on one stream are not handed to a kernel on another one)
+    key = (id(mask), t, b, tn, total, torch.cuda.current_stream().cuda_stream)
+    hit = _MASK_CACHE.get(key) if MASK_CACHE else None
     if hit is not None:
         ref, version, cached = hit
         if ref() is mask and version == mask._version:
@@ -176,9 +180,11 @@ def _pack_mask(mask, b, h, tn, total, device, transposed=False):
     _native.check(lib.ddp_attn_pack_mask(ctypes.c_void_p(mu8.data_ptr()), b, tn, total, m_ld, m_sb1,
                                          ctypes.c_void_p(bits.data_ptr()), t, _g._stream()))
     _native.count_launch()
-    if len(_MASK_CACHE) >= 4:
-        _MASK_CACHE.pop(next(iter(_MASK_CACHE)))
-    _MASK_CACHE[key] = (weakref.ref(mask), mask._version, bits)
+    if MASK_CACHE:
+        if len(_MASK_CACHE) >= 4:
+            _MASK_CACHE.pop(next(iter(_MASK_CACHE)))
+        # the entry (and its device memory) goes away with the mask tensor, not only on the next lookup
+        _MASK_CACHE[key] = (weakref.ref(mask, lambda _r, k=key: _MASK_CACHE.pop(k, None)), mask._version, bits)
     return bits, ldw, words // b
 
 
