@@ -588,7 +588,7 @@ extern "C" int ddp_attn_bwd_cols(const ddp_tensor* A, const ddp_tensor* G, const
   }
   const int sms = ddp_num_sms();
   if (!(p.dbg & 64)) {  // second generation: one 128-column block per item, P^T / dS^T stay in tensor memory
-    constexpr int kSmem2 = 4 * kAtTile + kAb2Stages * kAb2ColsStage + (2 * kAb2Stages + 12) * 8 + 16 + 1024;
+    constexpr int kSmem2 = 2 * kAtTile + kAb2ColsOut + kAb2ColsStages * kAb2ColsStage + (2 * kAb2ColsStages + 20) * 8 + 16 + 1024;
     static_assert(kSmem2 <= 232448, "shared memory budget exceeded");
     const long long items2 = (long long)world * p.b1 * n_mb * p.b0;
     int grid2 = world > 1 ? sms : (int)(items2 < sms ? items2 : sms);

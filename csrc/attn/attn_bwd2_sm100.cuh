@@ -53,7 +53,9 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd2_rows_kernel(const __g
   uint64_t* p_full = s_empty + 2;    // [2] dS_s written by all 8 warps of the stream
   uint64_t* o_done = p_full + 2;     // [2] dA += dS_s B_j finished (dS_s may be overwritten)
   uint64_t* o_final = o_done + 2;    // [1] the last product of the work item into dA finished
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_final + 1);
+  uint64_t* st_full = o_final + 1;   // [4] the quadrant's fp32 partial sums are staged (4 warps)
+  uint64_t* st_free = st_full + 4;   // [4] the store warp's copies have read them
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(st_free + 4);
 
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
   const int lane = threadIdx.x & 31;
@@ -410,19 +412,21 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd2_rows_kernel(const __g
 //   warps as in the row-side kernel; thread = one column j x 32 rows i
 // phase_mask bits: 1 = push the gathered operands, 2 = main loop, 4 = owner-side reduction (production: all).
 // ============================================================================================================
-constexpr int kAb2ColsStage = 2 * kAbHalfTile + 2048;  // A_i | dO_i | 64 x -L | 64 x -scale delta | mask 4 x 2 x 32 words
+constexpr int kAb2ColsStage = 2 * kAbHalfTile + 2048;
+constexpr int kAb2ColsStages = 7;
+constexpr int kAb2ColsOut = 4 * kAtTile;  // staging: 4 quadrants x (dV | dB) x 8 KB of fp32 partial sums  // A_i | dO_i | 64 x -L | 64 x -scale delta | mask 4 x 2 x 32 words
 
 template <int DT>
 __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd2_cols_kernel(const __grid_constant__ AttnBwdParams p) {
   using T = typename std::conditional<DT == DDP_BF16, __nv_bfloat16, __half>::type;
-  constexpr int STAGES = kAb2Stages;
+  constexpr int STAGES = kAb2ColsStages;  // not a power of two: slots by % STAGES
 
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sB = smem;                 // B block (128 rows x 128 bytes)
   uint8_t* sV = sB + kAtTile;         // V block
-  uint8_t* sOut = sV + kAtTile;       // dV | dB staging: 2 x 4 quadrants x 4 KB
-  uint8_t* sKV = sOut + 2 * kAtTile;  // STAGES x 18 KB
+  uint8_t* sOut = sV + kAtTile;       // dV | dB staging (16-bit results: 2 x 4 x 4 KB; fp32 partial sums: 4 x 2 x 8 KB)
+  uint8_t* sKV = sOut + kAb2ColsOut;  // STAGES x 18 KB
   uint64_t* bars = reinterpret_cast<uint64_t*>(sKV + STAGES * kAb2ColsStage);
   uint64_t* kv_full = bars;
   uint64_t* kv_empty = bars + STAGES;
@@ -433,7 +437,9 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd2_cols_kernel(const __g
   uint64_t* p_full = s_empty + 2;    // [2] P^T_s and dS^T_s written by all 8 warps of the stream
   uint64_t* o_done = p_full + 2;     // [2] the two products of the stream's step finished
   uint64_t* o_final = o_done + 2;    // [1] the last products of the work item finished
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_final + 1);
+  uint64_t* st_full = o_final + 1;   // [4] the quadrant's fp32 partial sums are staged (4 warps)
+  uint64_t* st_free = st_full + 4;   // [4] the store warp's copies have read them
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(st_free + 4);
 
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
   const int lane = threadIdx.x & 31;
@@ -473,6 +479,10 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd2_cols_kernel(const __g
       mbar_init(&o_done[s], 1);
     }
     mbar_init(o_final, 1);
+    for (int s = 0; s < 4; ++s) {
+      mbar_init(&st_full[s], 4);
+      mbar_init(&st_free[s], 1);
+    }
     fence_mbar_init();
   }
   if (warp == 2) tmem_alloc(tmem_slot, 512);
@@ -529,7 +539,7 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd2_cols_kernel(const __g
         const long long cg0 = static_cast<long long>(seg) * p.Tn + c0;
         if (p.mask_bits != nullptr) mask_groups = min(4, (p.Tn - c0 + 31) / 32);
         for (int nb = 0; nb < nj; ++nb, ++g) {
-          const uint32_t slot = g & (STAGES - 1);
+          const uint32_t slot = g % STAGES;
           mbar_wait(&kv_empty[slot], ((g / STAGES) & 1) ^ 1, 72);
           uint8_t* sb = sKV + slot * kAb2ColsStage;
           const int i0 = nb * kAbStep;
@@ -562,7 +572,7 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd2_cols_kernel(const __g
       uint32_t a_ph = 0, pf_ph0 = 0, pf_ph1 = 0, se_ph0 = 0, se_ph1 = 0;
       uint32_t g0 = 0;
       auto issue_sp = [&](uint32_t g, int s) {  // S^T_s, dP^T_s of the step with running count g
-        const uint32_t slot = g & (STAGES - 1);
+        const uint32_t slot = g % STAGES;
         mbar_wait(&kv_full[slot], (g / STAGES) & 1, 73);
         tc_fence_after();
         const uint64_t da = umma_smem_desc(sKV_u + slot * kAb2ColsStage, 16, 1024);
@@ -582,7 +592,7 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd2_cols_kernel(const __g
         mbar_wait(&p_full[s], s ? pf_ph1 : pf_ph0, 75);
         if (s) pf_ph1 ^= 1; else pf_ph0 ^= 1;
         tc_fence_after();
-        const uint32_t slot = g & (STAGES - 1);
+        const uint32_t slot = g % STAGES;
         const uint64_t da = umma_smem_desc(sKV_u + slot * kAb2ColsStage, kAbHalfTile, 1024, 2);  // A_i [K = i][N = d]
         const uint64_t dg = umma_smem_desc(sKV_u + slot * kAb2ColsStage + kAbHalfTile, kAbHalfTile, 1024, 2);
         const uint32_t tPt = tmem_base + 384 + s * 32, tDt = tmem_base + 448 + s * 32;
@@ -617,6 +627,42 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd2_cols_kernel(const __g
       }
     } else if (warp == 2) {
       if (dist && do_push) attn_push_gather(p, Bt, lane);
+    } else if (dist && !(p.dbg & 2048) && lane < 4) {
+      // ===================================================== store warp: lane q moves the blocks of quadrant q
+      const int q = lane;
+      uint32_t sf_ph = 0;
+      uint32_t done_ok = 0;  // peers whose done counter this lane has already checked
+      const uint32_t sbufq = smem_u32(sOut) + q * 16384;
+      for (int it = blockIdx.x; it < items; it += gridDim.x) {
+        int seg, b1i, b0i, c0;
+        decode(it, seg, b1i, b0i, c0);
+        const int b = b1i * p.b0 + b0i;
+        const int col0 = c0 + q * 32;
+        const int rows_valid = max(0, min(32, p.Tn - col0));
+        if (seg != p.rank && !(done_ok & (1u << seg))) {  // the owner has finished reading its slots of two calls ago
+          wait_flag_ge(p.done[p.rank] + seg, p.seq - 2u, p.status, 4);
+          done_ok |= 1u << seg;
+        }
+        mbar_wait(&st_full[q], sf_ph, 82);
+        sf_ph ^= 1;
+        if (rows_valid > 0) {
+#pragma unroll
+          for (int kind = 0; kind < 2; ++kind) {
+            const uint32_t row_bytes = static_cast<uint32_t>(kind ? p.d : p.dv) * 4u;
+            char* dst = p.ws[(p.dbg & 16384) ? p.rank : seg] + (kind ? p.ws_p1_off : p.ws_p0_off) +  // 16384: timing only
+                        ((static_cast<size_t>(p.rank) * Bt + b) * p.Tn + col0) * static_cast<size_t>(row_bytes);
+            bulk_store_1d(dst, sbufq + kind * 8192, static_cast<uint32_t>(rows_valid) * row_bytes);
+          }
+          bulk_commit_group();
+          bulk_wait_group_read<0>();
+        }
+        mbar_arrive(&st_free[q]);
+        if (rows_valid > 0) bulk_wait_group<0>();
+        fence_proxy_async();
+        const size_t fidx = static_cast<size_t>(p.rs_flag_off) +
+                            (((static_cast<size_t>(p.rank) * Bt + b) * n_mb + c0 / kAtBM) * 4 + q) * 4;
+        st_release_sys(p.flags[seg] + fidx, p.seq);  // one flag per (source, batch, block, quadrant)
+      }
     }
   } else {
     setmaxnreg_inc<kAtRegsHigh>();
@@ -638,8 +684,7 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd2_cols_kernel(const __g
     const uint32_t quad_bar = 1 + q;
     uint32_t sf_ph = 0, of_ph = 0, od_ph = 0;
     uint32_t g0 = 0;
-    uint32_t done_ok = 0;  // peers whose done counter this warp has already checked
-    uint32_t* pend_flag = nullptr;  // reduce-scatter flag of the previous work item, not yet published
+    uint32_t sfree_ph = 0;
     for (int it = blockIdx.x; it < items; it += gridDim.x) {
       int seg, b1i, b0i, c0;
       decode(it, seg, b1i, b0i, c0);
@@ -649,7 +694,7 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd2_cols_kernel(const __g
       bool sf_ok = false;
       for (int j = s; j < nj; j += 2) {
         const int nvalid = p.M - (j * kAbStep + h * 32);  // live rows of this thread's half
-        const uint32_t slot_off = ((g0 + j) & (STAGES - 1)) * kAb2ColsStage;
+        const uint32_t slot_off = ((g0 + j) % STAGES) * kAb2ColsStage;
         if (!sf_ok) mbar_wait(&s_full[s], sf_ph, 77);
         sf_ph ^= 1;
         tc_fence_after();
@@ -765,26 +810,18 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd2_cols_kernel(const __g
           __syncwarp();
         }
         named_bar_sync(quad_bar, 128);  // the staging tiles belong to the next work item again
+      } else if (p.dbg & 2048) {
+        named_bar_sync(quad_bar, 128);  // ablation (timing only): no partial sums leave, no reduction
       } else {
-        // fp32 partial sums -> the owner's slot [src = this rank][b][Tn][cols]; one flag per (block, quadrant, part)
-        if (seg != p.rank && !(done_ok & (1u << seg))) {
-          if (lane == 0) wait_flag_ge(p.done[p.rank] + seg, p.seq - 2u, p.status, 4);
-          __syncwarp();
-          done_ok |= 1u << seg;
-        }
-        if (pend_flag != nullptr) {  // the previous block's copies have had a whole work item to complete
-          bulk_wait_group<0>();
-          fence_proxy_async();
-          __threadfence_system();
-          st_release_sys(pend_flag, p.seq);
-          pend_flag = nullptr;
-        }
-        __syncwarp();
-        // The 32 columns of a lane quadrant are 32 consecutive rows of the owner's [Tn][cols] fp32 slot, i.e. ONE
-        // contiguous block: the four warps of the quadrant stage their 16-column parts in shared memory and one
-        // bulk copy (TMA engine, shared -> peer memory) moves the block.  (Per-thread 16-byte stores, lanes a row
-        // apart, crossed NVLink as 16-byte packets and cost ~0.4 ms per remote segment at the flagship shape.)
-        const uint32_t sbufq = smem_u32(sOut) + q * 8192;
+        // fp32 partial sums -> the owner's slot [src = this rank][b][Tn][cols].  The 32 columns of a lane quadrant
+        // are 32 consecutive rows of that slot, i.e. ONE contiguous block per result: the four warps of the
+        // quadrant stage their 16-column parts of dV and dB in shared memory and hand the blocks to the store warp
+        // (warp 3), which moves them with bulk copies (TMA engine, shared -> peer memory), waits for them and
+        // publishes the flag.  Nothing here waits for a copy, a system-scope fence or another warp: those cost
+        // ~13 us per work item when the elementwise warps did them (all CTAs reach this point together).
+        mbar_wait(&st_free[q], sfree_ph ^ 1, 81);  // the copies of the previous work item have read the staging blocks
+        sfree_ph ^= 1;
+        const uint32_t sbufq = smem_u32(sOut) + q * 16384;
 #pragma unroll
         for (int kind = 0; kind < 2; ++kind) {
           const int ncols = kind ? p.d : p.dv;
@@ -796,43 +833,20 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd2_cols_kernel(const __g
 #pragma unroll
           for (int c = 0; c < 4; ++c)
             if (part * 16 + c * 4 < ncols)
-              st_shared_v4(sbufq + lane * row_bytes + part * 64 + c * 16,
+              st_shared_v4(sbufq + kind * 8192 + lane * row_bytes + part * 64 + c * 16,
                            make_uint4(ra[4 * c], ra[4 * c + 1], ra[4 * c + 2], ra[4 * c + 3]));
-          tc_fence_before();
-          fence_proxy_async_smem();
-          named_bar_sync(quad_bar, 128);  // the block is staged (and all four warps have read this accumulator)
-          if (part == 0 && rows_valid > 0) {
-            if (lane == 0) {
-              char* dst = p.ws[seg] + (kind ? p.ws_p1_off : p.ws_p0_off) +
-                          ((static_cast<size_t>(p.rank) * Bt + b) * p.Tn + col0) * static_cast<size_t>(row_bytes);
-              bulk_store_1d(dst, sbufq, static_cast<uint32_t>(rows_valid) * row_bytes);
-              bulk_commit_group();
-              bulk_wait_group_read<0>();  // the staging block has been read; the writes are still in flight
-            }
-            __syncwarp();
-          }
-          named_bar_sync(quad_bar, 128);  // the staging block may be overwritten
         }
-        // The flag of this block is published one work item later (or after the last one), once its bulk copies
-        // have completed: waiting for a copy across NVLink here would stall all 16 warps for its whole flight
-        // time (all CTAs push at the same moments, ~14 us per 64 KB block at the flagship shape).
-        if (part == 0 && lane == 0) {
-          const size_t fidx = static_cast<size_t>(p.rs_flag_off) +
-                              (((static_cast<size_t>(p.rank) * Bt + b) * n_mb + c0 / kAtBM) * 4 + q) * 4;
-          pend_flag = p.flags[seg] + fidx;  // one flag per (source, batch, block, quadrant)
-        }
+        tc_fence_before();
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&st_full[q]);
+        // the next work item's first accumulating MMA follows a step of EACH stream, i.e. every warp's reads above,
+        // unless the item has a single step
+        if (nj < 2) named_bar_sync(quad_bar, 128);
       }
     }
-    if (pend_flag != nullptr) {  // (lane 0 of the part-0 warps only)
-      bulk_wait_group<0>();
-      fence_proxy_async();
-      __threadfence_system();
-      st_release_sys(pend_flag, p.seq);
-      pend_flag = nullptr;
-    }
-    __syncwarp();
     // ---------------------------------------------------- reduce-scatter: owner-side reduction
-    if (dist && do_reduce) {
+    if (dist && do_reduce && !(p.dbg & (2048 | 4096))) {  // 4096: ablation (timing only), partials leave but nobody reduces
       const int r_items = Bt * n_mb * 16;
       const uint32_t* my_flags = p.flags[p.rank] + p.rs_flag_off;
       for (int item = blockIdx.x * 16 + idx; item < r_items; item += gridDim.x * 16) {
