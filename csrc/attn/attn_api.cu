@@ -255,7 +255,11 @@ static int attn_bwd_comm(AttnBwdParams& p, const ddp_tensor* B, const ddp_tensor
     uint64_t gd[5] = {(uint64_t)t->cols, 1, (uint64_t)t->rows, Bt, (uint64_t)world};
     uint64_t gs[4] = {row_bytes, row_bytes, row_bytes * t->rows, row_bytes * t->rows * Bt};
     uint32_t box[5] = {64, 1, box_rows, 1, 1};
-    char* base = static_cast<char*>(comm->ws[rank]) + (i ? p.ws_v_off : 0);
+    // second-generation kernels only: a still valid gather of the same operands (ddp_comm::gather_ws) is read in place
+    const bool reuse = comm->gather_ws != nullptr && !(p.dbg & 64);
+    p.gather_ready = reuse ? 1 : 0;
+    char* base = (reuse ? static_cast<char*>(const_cast<void*>(comm->gather_ws)) : static_cast<char*>(comm->ws[rank])) +
+                 (i ? p.ws_v_off : 0);
     if (int e = make_map(i ? &p.tmVg : &p.tmBg, t->dtype, base, gd, gs, box, false)) return e;
     p.push_src[i] = static_cast<const char*>(t->ptr);
     p.push_ld[i] = t->ld * 2; p.push_sb0[i] = t->sb0 * 2; p.push_sb1[i] = t->sb1 * 2;

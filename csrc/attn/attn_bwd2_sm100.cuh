@@ -142,7 +142,7 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd2_rows_kernel(const __g
           const int seg = (p.rank + si) % p.world;
           const bool remote = dist && seg != p.rank;
           bool need_fence = false;
-          if (remote) {
+          if (remote && !p.gather_ready) {
             attn_wait_gathered(p, Bt, seg, b, lane);
             need_fence = true;
           }
@@ -247,7 +247,7 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd2_rows_kernel(const __g
         g0 += static_cast<uint32_t>(nj);
       }
     } else if (warp == 2) {
-      if (dist && do_produce) attn_push_gather(p, Bt, lane);
+      if (dist && do_produce && !p.gather_ready) attn_push_gather(p, Bt, lane);
     }
   } else {
     setmaxnreg_inc<kAtRegsHigh>();
@@ -517,7 +517,7 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd2_cols_kernel(const __g
         decode(it, seg, b1i, b0i, c0);
         const int b = b1i * p.b0 + b0i;
         const bool remote = dist && seg != p.rank;
-        if (remote) {
+        if (remote && !p.gather_ready) {
           attn_wait_gathered(p, Bt, seg, b, lane);
           fence_proxy_async();
         }
@@ -626,7 +626,7 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd2_cols_kernel(const __g
         g0 += static_cast<uint32_t>(nj);
       }
     } else if (warp == 2) {
-      if (dist && do_push) attn_push_gather(p, Bt, lane);
+      if (dist && do_push && !p.gather_ready) attn_push_gather(p, Bt, lane);
     } else if (dist && !(p.dbg & 2048) && lane < 4) {
       // ===================================================== store warp: lane q moves the blocks of quadrant q
       const int q = lane;

@@ -61,6 +61,7 @@ struct alignas(64) AttnBwdParams {
   const char* push_src[2];
   long long push_ld[2], push_sb0[2], push_sb1[2];
   int push_rows, push_row_bytes[2];
+  int gather_ready;  // the gathered B / V are already complete in the workspace the gather maps point at
   int dbg;
 };
 

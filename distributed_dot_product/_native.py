@@ -30,7 +30,7 @@ class Comm(ctypes.Structure):
                 ('phase_mask', ctypes.c_int32), ('chunk_rows', ctypes.c_int32), ('_pad', ctypes.c_int32),
                 ('ws', ctypes.c_void_p * MAX_WORLD), ('flags', ctypes.c_void_p * MAX_WORLD),
                 ('done', ctypes.c_void_p * MAX_WORLD), ('exit_counter', ctypes.c_void_p),
-                ('status', ctypes.c_void_p), ('mc_ws', ctypes.c_void_p)]
+                ('status', ctypes.c_void_p), ('mc_ws', ctypes.c_void_p), ('gather_ws', ctypes.c_void_p)]
 
 
 class Epilogue(ctypes.Structure):

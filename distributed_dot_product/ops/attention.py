@@ -188,13 +188,27 @@ def _pack_mask(mask, b, h, tn, total, device, transposed=False):
     return bits, ldw, words // b
 
 
+#: the backward kernels read the forward's all-gather of q / v in place when nothing else has used the symmetric
+#: heap since (``DDP_GATHER_REUSE=0``: every kernel gathers for itself)
+GATHER_REUSE = bool(int(__import__('os').environ.get('DDP_GATHER_REUSE', '1')))
+#: how many backward passes skipped their two all-gathers (tests)
+gather_reuse_count = 0
+
+
 def flash_attention_backward(k4, q4, v4, g4, neg_lse, nds, mask, scale, offset, dk4, dq4, dv4, bits=None,
-                             which=3):
+                             which=3, gather_tag=None):
     """Backward of ``flash_attention_forward`` without any ``[T/N, T]`` slab: two deterministic kernels recompute
     the probability tiles from the forward's log-sum-exp (``neg_lse = -L``, ``nds = -scale * rowsum(dO * O)``,
     both fp32 ``[B, H, stat_ld]`` with ``stat_ld`` a multiple of 64).  ``dk4`` gets the row-side gradient
     (all-gather of q / v fused in), ``dq4`` / ``dv4`` the column-side ones (all-gather AND the reduce-scatter of
-    the ranks' partial sums fused in).  ``which``: bit 0 = row-side kernel, bit 1 = column-side kernel (tools)."""
+    the ranks' partial sums fused in).  ``which``: bit 0 = row-side kernel, bit 1 = column-side kernel (tools).
+
+    ``gather_tag`` = ``(heap generation, sequence number)`` of the forward call that gathered these very ``q4`` /
+    ``v4``: if no collective call has touched the symmetric heap since, its workspace parity still holds the complete
+    gather and both kernels read it in place (no pushes, no flag waits: 2 x (N-1)/N x |q, v| less NVLink traffic
+    and no start-up stall).  Safe under the epoch protocol: the row-side call (seq + 1) only READS the forward's
+    parity, the column-side call (seq + 2) owns that parity anyway, and the next call that pushes into it
+    (>= seq + 4) waits for every peer's seq + 2."""
     import ctypes
     from distributed_dot_product.parallel import runtime
     lib = _native.load()
@@ -215,26 +229,41 @@ def flash_attention_backward(k4, q4, v4, g4, neg_lse, nds, mask, scale, offset, 
     nl, nd = ctypes.c_void_p(neg_lse.data_ptr()), ctypes.c_void_p(nds.data_ptr())
     chunk = _g.chunk_rows_from_offset(offset, q4.size(-2), 2 * b * h)
 
-    def comm_for(ws_fn):
+    reuse_ws = None
+    if world > 1:
+        # both kernels' needs first: growing the heap re-allocates it (and would drop a gather we mean to reuse)
+        hp = runtime.heap()
+        need_ws = need_flags = 0
+        for bit, ws_fn in ((1, lib.ddp_attn_fwd_workspace), (2, lib.ddp_attn_bwd_cols_workspace)):
+            if which & bit:
+                ws, nf = ctypes.c_size_t(), ctypes.c_size_t()
+                _native.check(ws_fn(ctypes.byref(vb), ctypes.byref(vv), world, chunk, ctypes.byref(ws),
+                                    ctypes.byref(nf)))
+                need_ws, need_flags = max(need_ws, ws.value), max(need_flags, nf.value)
+        hp.ensure(need_ws, need_flags)
+        if GATHER_REUSE and which == 3 and gather_tag is not None and gather_tag == (hp.generation, hp.seq):
+            reuse_ws = hp.comm[hp.seq & 1].ws[runtime.get_rank()]
+            global gather_reuse_count
+            gather_reuse_count += 1
+
+    def comm_for():
         if world == 1:
             return None
-        ws, nf = ctypes.c_size_t(), ctypes.c_size_t()
-        _native.check(ws_fn(ctypes.byref(vb), ctypes.byref(vv), world, chunk, ctypes.byref(ws), ctypes.byref(nf)))
-        hp = runtime.heap()
-        hp.ensure(ws.value, nf.value)
-        return ctypes.byref(hp.next_comm(chunk))
+        cm = hp.next_comm(chunk)
+        cm.gather_ws = reuse_ws
+        return ctypes.byref(cm)
 
     if which & 1:
         _native.check(lib.ddp_attn_bwd_rows(
             ctypes.byref(va), ctypes.byref(vg), ctypes.byref(vb), ctypes.byref(vv), ctypes.byref(vda), nl, nd, stat_ld,
             ctypes.c_void_p(bits.data_ptr()) if bits is not None else None, ldw, sb1w, float(scale),
-            comm_for(lib.ddp_attn_fwd_workspace), 0, _g._stream()))
+            comm_for(), 0, _g._stream()))
         _native.count_launch()
     if which & 2:
         _native.check(lib.ddp_attn_bwd_cols(
             ctypes.byref(va), ctypes.byref(vg), ctypes.byref(vb), ctypes.byref(vv), ctypes.byref(vdv), ctypes.byref(vdb),
             nl, nd, stat_ld, ctypes.c_void_p(bits_t.data_ptr()) if bits_t is not None else None, ldwt, sb1wt,
-            float(scale), comm_for(lib.ddp_attn_bwd_cols_workspace), 0, _g._stream()))
+            float(scale), comm_for(), 0, _g._stream()))
         _native.count_launch()
 
 
@@ -328,6 +357,10 @@ class _FlashAttentionCore(torch.autograd.Function):
                                       bits=bits)
         ctx.save_for_backward(keys, queries, values, out, lse, mask, bits)
         ctx.num_heads, ctx.scale, ctx.offset = num_heads, scale, offset
+        ctx.gather_tag = None
+        if runtime.get_world_size() > 1:
+            hp = runtime.heap()
+            ctx.gather_tag = (hp.generation, hp.seq)   # the call that gathered queries / values
         return out
 
     @staticmethod
@@ -351,7 +384,7 @@ class _FlashAttentionCore(torch.autograd.Function):
         d_keys, d_queries, d_values = torch.empty_like(keys), torch.empty_like(queries), torch.empty_like(values)
         flash_attention_backward(_heads(keys, h), _heads(queries, h), _heads(values, h), _heads(grad_out, h),
                                  neg_lse, nds, mask, scale, offset, _heads(d_keys, h), _heads(d_queries, h),
-                                 _heads(d_values, h), bits=bits)
+                                 _heads(d_values, h), bits=bits, gather_tag=ctx.gather_tag)
         return d_keys, d_queries, d_values, None, None, None, None
 
 

@@ -376,6 +376,7 @@ class _Heap(object):
         cm = self.comm[self.seq & 1]
         cm.seq = self.seq
         cm.chunk_rows = int(chunk_rows)
+        cm.gather_ws = None
         return cm
 
     def _poll_status(self, stream):

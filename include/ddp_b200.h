@@ -55,6 +55,9 @@ typedef struct ddp_comm {
                                     exceeds 20 s stores which wait (1..5) here instead of hanging; may be NULL */
   void* mc_ws;                   /* NVSwitch multicast alias of the workspace (ddp_mc_bind): a store to mc_ws + off
                                     lands at ws[r] + off of EVERY rank; NULL = push to each peer separately */
+  const void* gather_ws;         /* attention backward only: this rank's workspace (of EITHER parity) that still holds
+                                    the complete all-gather of exactly these B / V operands (the forward's); the
+                                    kernel then neither pushes nor waits for them.  NULL = gather in this call */
 } ddp_comm;
 
 const char* ddp_last_error(void);

@@ -196,6 +196,20 @@ def _module_flash_dense_twin(rank, world):
             for (n, p), (_, pr) in zip(model.named_parameters(), twin.named_parameters()):
                 e = (p.grad.float() - pr.grad).abs().max().item() / max(pr.grad.abs().max().item(), 0.05 * gscale)
                 assert e < 4e-2, (kind, step, n, e)
+    # from the second step on (heap at its final size) the backward kernels read the forward's all-gather in place;
+    # the result is bit-identical to gathering again in both kernels
+    assert att.gather_reuse_count >= 2, att.gather_reuse_count
+    grads = []
+    for reuse in (True, False, True):
+        att.GATHER_REUSE = reuse
+        n0 = att.gather_reuse_count
+        k.grad = q.grad = None
+        model(k, q, k, gmask[:, rows].contiguous()).float().sum().backward()
+        assert att.gather_reuse_count == n0 + int(reuse)
+        grads.append((k.grad.clone(), q.grad.clone()))
+    check_status()
+    for kg_, qg_ in grads[1:]:
+        assert torch.equal(kg_, grads[0][0]) and torch.equal(qg_, grads[0][1])
 
 
 @pytest.mark.parametrize('world', [2, 4, 8])
