@@ -41,6 +41,9 @@ def parse():
     ap.add_argument('--d-model', type=int, default=D_MODEL)
     ap.add_argument('--offset', type=int, default=1024)
     ap.add_argument('--dtype', type=str, default='bf16', help='ours: bf16 | fp16 | fp32 (fp32 storage, TF32 math)')
+    ap.add_argument('--compute-dtype', type=str, default='', choices=['', 'bf16', 'fp16'],
+                    help='ours, with --dtype fp32: mixed precision - fp32 parameters / activations, 16-bit math on the '
+                         'slab-free kernels (DistributedDotProductAttn(compute_dtype=...))')
     ap.add_argument('--ref-autocast', type=str, default='none', choices=['none', 'bf16'],
                     help='reference arm: run the stock module inside torch.autocast(cuda, bfloat16)')
     ap.add_argument('--mask', type=str, default='zeros', choices=['none', 'zeros', 'causal', 'random'],
@@ -165,7 +168,13 @@ def main():
     total_t = args.T if args.T else ROWS_PER_GPU * world
     tn = total_t // world
     torch.manual_seed(111)
-    model = DistributedDotProductAttn(args.d_model, num_heads=args.heads, offset=args.offset).to(dev, dtype)
+    mixed = None
+    if not reference and args.compute_dtype:
+        if dtype != torch.float32:
+            raise SystemExit('--compute-dtype goes with --dtype fp32')
+        mixed = {'bf16': torch.bfloat16, 'fp16': torch.float16}[args.compute_dtype]
+    model = DistributedDotProductAttn(args.d_model, num_heads=args.heads, offset=args.offset,
+                                      **({'compute_dtype': mixed} if mixed is not None else {})).to(dev, dtype)
     if world > 1:
         for p in model.parameters():
             dist.broadcast(p.data, src=0)
@@ -277,6 +286,8 @@ def main():
                 att.FLASH_TRAIN = bool(flag.item() > 0)
                 attention_path = 'slab-free (flash)' if att.FLASH_TRAIN else 'slab (self-check rejected slab-free path)'
                 torch.cuda.empty_cache()
+            elif mixed is not None:
+                attention_path = 'slab-free (flash), fp32 parameters and activations cast per call'
             elif dtype == torch.float32:
                 attention_path = 'slab (fp32 storage, TF32 tensor-core math)'
         torch.cuda.reset_peak_memory_stats()  # the self-check's slab step must not count as this path's peak
@@ -323,7 +334,8 @@ def main():
             'work_normalised_ms': ms / world,  # per-GPU attention work grows with N at fixed rows per GPU
             'dtype': (('bf16 autocast over fp32 weights (stock reference module under torch.autocast)' if autocast
                        else 'fp32 storage, tf32 matmul (reference native dtype)') if reference
-                      else ('fp32 storage, tf32 matmul' if args.dtype == 'fp32' else args.dtype)),
+                      else (('fp32 storage, %s math (mixed precision)' % args.compute_dtype) if args.compute_dtype
+                            else 'fp32 storage, tf32 matmul' if args.dtype == 'fp32' else args.dtype)),
             'data': 'synthetic',
             'config': {'model': 'DistributedDotProductAttn heads=%d d_model=%d' % (args.heads, args.d_model),
                        'global_batch': 1, 'seq_len': total_t, 'rows_per_gpu': tn,

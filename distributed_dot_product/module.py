@@ -25,7 +25,8 @@ from distributed_dot_product.ops.linear import linear
 
 class DistributedDotProductAttn(nn.Module):
     def __init__(self, key_dim: int, value_dim: int = None, query_dim: int = None, num_heads: int = 1,
-                 add_bias: bool = False, offset: int = 32, distributed: bool = True):
+                 add_bias: bool = False, offset: int = 32, distributed: bool = True,
+                 compute_dtype: torch.dtype = None):
         super(DistributedDotProductAttn, self).__init__()
         assert key_dim % num_heads == 0
         value_dim = value_dim if value_dim is not None else key_dim
@@ -39,6 +40,13 @@ class DistributedDotProductAttn(nn.Module):
         self.value_dim = value_dim
         self.offset = offset
         self.distributed = distributed
+        # Mixed precision (not in the reference, whose ops fail under autocast): fp32 parameters and activations,
+        # bf16 / fp16 tensor-core math.  The inputs and the four weights are cast once per call and everything
+        # between them runs on the slab-free 16-bit kernels; the output comes back in the input dtype and the
+        # parameter gradients in fp32.  ``None`` follows ``torch.autocast('cuda', ...)`` when that is active.
+        if compute_dtype not in (None, torch.bfloat16, torch.float16):
+            raise ValueError('compute_dtype must be None, torch.bfloat16 or torch.float16')
+        self.compute_dtype = compute_dtype
         self.dim = key_dim // self.num_heads
         self.keys = nn.Linear(key_dim, key_dim, bias=add_bias)
         self.queries = nn.Linear(query_dim, key_dim, bias=add_bias)
@@ -56,6 +64,26 @@ class DistributedDotProductAttn(nn.Module):
         scale = 1.0 / math.sqrt(self.dim)
         if self._native_path(keys) and keys.dim() == 3:
             # ---- B200 path: every stage is a hand-written sm_100a kernel
+            cd = self.compute_dtype
+            if cd is None and torch.is_autocast_enabled('cuda'):
+                cd = torch.get_autocast_dtype('cuda')
+                cd = cd if cd in (torch.bfloat16, torch.float16) else None
+            if cd is not None and keys.dtype == torch.float32:
+                seen = {}
+
+                def low(t):  # one cast per distinct tensor (self-attention passes the same one three times)
+                    if t is None:
+                        return None
+                    if id(t) not in seen:
+                        seen[id(t)] = t.to(cd)
+                    return seen[id(t)]
+
+                k = linear(low(keys), low(self.keys.weight), low(self.keys.bias))
+                q = linear(low(queries), low(self.queries.weight), low(self.queries.bias))
+                v = linear(low(values), low(self.values.weight), low(self.values.bias))
+                o = attention_core(k, q, v, attn_mask, self.num_heads, scale, self.offset)
+                o = linear(o, low(self.composition.weight), low(self.composition.bias))
+                return o if self.compute_dtype is None else o.to(keys.dtype)   # autocast keeps the low dtype
             k = linear(keys, self.keys.weight, self.keys.bias)
             q = linear(queries, self.queries.weight, self.queries.bias)
             v = linear(values, self.values.weight, self.values.bias)

@@ -176,6 +176,48 @@ def test_module_vs_dense_twin_world1(cuda_device, dtype, heads, bias):
         assert rel < (2e-2 if dtype == torch.float32 else 6e-2), (n, rel)
 
 
+@pytest.mark.parametrize('mode', ['compute_dtype', 'autocast'])
+def test_module_mixed_precision_world1(cuda_device, mode):
+    """fp32 parameters and activations, bf16 math on the slab-free kernels (``compute_dtype`` / ``torch.autocast``):
+    output and every gradient against the fp32 dense twin, gradients arrive in fp32, the 16-bit kernels ran."""
+    import distributed_dot_product.ops.attention as att
+    from distributed_dot_product import _native
+    from distributed_dot_product.module import DistributedDotProductAttn
+    torch.manual_seed(6)
+    dim, t, heads = 256, 160, 4
+    cd = torch.bfloat16 if mode == 'compute_dtype' else None
+    model = DistributedDotProductAttn(dim, num_heads=heads, add_bias=True, compute_dtype=cd).to(cuda_device)
+    twin = DistributedDotProductAttn(dim, num_heads=heads, add_bias=True, distributed=False).to(cuda_device)
+    twin.load_state_dict(model.state_dict())
+    x = torch.rand(1, t, dim, device=cuda_device, requires_grad=True)
+    mask = torch.triu(torch.ones(t, t, dtype=torch.bool, device=cuda_device), diagonal=1).unsqueeze(0)
+    calls = []
+    core = att._FlashAttentionCore.apply
+    att._FlashAttentionCore.apply = staticmethod(lambda *a: (calls.append(a[0].dtype), core(*a))[1])
+    try:
+        if mode == 'autocast':
+            with torch.autocast('cuda', dtype=torch.bfloat16):
+                out = model(x, x, x, mask)
+            assert out.dtype == torch.bfloat16
+        else:
+            out = model(x, x, x, mask)
+            assert out.dtype == torch.float32
+        out.float().sum().backward()
+    finally:
+        del att._FlashAttentionCore.apply   # back to the inherited classmethod
+    assert calls == [torch.bfloat16]
+    xr = x.detach().clone().requires_grad_(True)
+    ref = twin(xr, xr, xr, mask)
+    ref.sum().backward()
+    assert (out.float() - ref).abs().max().item() < 4e-2
+    assert x.grad.dtype == torch.float32 and (x.grad - xr.grad).abs().max().item() < 0.16
+    gscale = max(pr.grad.abs().max().item() for pr in twin.parameters())
+    for (n, p), (_, pr) in zip(model.named_parameters(), twin.named_parameters()):
+        assert p.grad.dtype == torch.float32, n
+        rel = (p.grad - pr.grad).abs().max().item() / max(pr.grad.abs().max().item(), 0.05 * gscale)
+        assert rel < 6e-2, (n, rel)
+
+
 def test_autograd_ops_world1(cuda_device):
     from distributed_dot_product.multiplication.ops import (
         FullMultiplication, LeftTransposeMultiplication, RightTransposeMultiplication)
