@@ -41,6 +41,8 @@ def parse():
     ap.add_argument('--d-model', type=int, default=D_MODEL)
     ap.add_argument('--offset', type=int, default=1024)
     ap.add_argument('--dtype', type=str, default='bf16', help='ours: bf16 | fp16 | fp32 (fp32 storage, TF32 math)')
+    ap.add_argument('--graph', type=str, default='auto', choices=['auto', 'off'],
+                    help='ours, 1 GPU: replay the whole step from a CUDA graph (utils.graphs.GraphedStep)')
     ap.add_argument('--compute-dtype', type=str, default='', choices=['', 'bf16', 'fp16'],
                     help='ours, with --dtype fp32: mixed precision - fp32 parameters / activations, 16-bit math on the '
                          'slab-free kernels (DistributedDotProductAttn(compute_dtype=...))')
@@ -297,25 +299,81 @@ def main():
         # ---------------- device-timed region
         sampler = ClockSampler(physical_gpu_index(local_rank))
         sampler.start()
+        # one GPU: the step is replayed from a CUDA graph (one launch instead of ~26); the launch count is taken
+        # from an eager step
+        graphed = None
+        use_graph = (not reference and world == 1 and args.graph == 'auto' and not args.mask_refresh)
+        run_dev = lambda: step(x_dev, y_dev)  # noqa: E731
+        per_step_launches = None
+        if use_graph:
+            try:
+                from distributed_dot_product.utils.graphs import GraphedStep
+                l0 = count_launches.launch_count
+                step(x_dev, y_dev)
+                per_step_launches = count_launches.launch_count - l0
+                graphed = GraphedStep(lambda: step(x_dev, y_dev))
+                eager_loss = step(x_dev, y_dev).item()
+                if abs(graphed().item() - eager_loss) > 1e-3 * abs(eager_loss) + 1e-12:
+                    raise RuntimeError('graph replay and eager step disagree')
+                run_dev = graphed
+            except Exception as e:  # noqa: BLE001 - any capture problem: time the eager step
+                sys.stderr.write('CUDA graph capture failed, timing the eager step: %s\n' % e)
+                graphed = None
+                torch.cuda.synchronize()
         l0 = count_launches.launch_count if count_launches else 0
-        ms = timed_steps(lambda: step(x_dev, y_dev))
+        ms = timed_steps(run_dev)
         launches = (count_launches.launch_count - l0) if count_launches else None
+        if graphed is not None:
+            launches = per_step_launches * args.steps
         sampler.stop_flag.set()
         sampler.join()
-        # ---------------- end-to-end region: H2D of the step inputs + D2H of the loss, every step
-        x_in = torch.empty_like(x_dev)
-        y_in = torch.empty_like(y_dev)
-        for _ in range(2):
-            x_in.copy_(x_host, non_blocking=True)
-            y_in.copy_(y_host, non_blocking=True)
-            loss_host.copy_(step(x_in, y_in).detach().reshape(1), non_blocking=True)
-        barrier()
+        # ---------------- end-to-end region: H2D of the step inputs + D2H of the loss, every step.
+        # Input pipeline (both arms): two device buffers; the inputs of step i + 1 cross PCIe on a copy stream while
+        # step i computes (every step still copies its own inputs from pinned memory inside the timed region; the
+        # first timed step pays its copy in full, the last one prefetches a batch nobody uses).
+        copy_stream = torch.cuda.Stream()
+        bufs = [(torch.empty_like(x_dev), torch.empty_like(y_dev)) for _ in range(2)]
+        ready = [None, None]   # copy of the buffer pair finished (copy stream)
+        done = [None, None]    # last step that read the buffer pair finished (compute stream)
+        pipe = {'i': 0}
+        run_pair = [lambda: step(*bufs[0]), lambda: step(*bufs[1])]
+        if graphed is not None:
+            try:
+                run_pair = [GraphedStep(run_pair[0]), GraphedStep(run_pair[1])]
+            except Exception as e:  # noqa: BLE001
+                sys.stderr.write('CUDA graph capture failed for the end-to-end step: %s\n' % e)
+                torch.cuda.synchronize()
+
+        def prefetch(i):
+            if done[i & 1] is not None:
+                copy_stream.wait_event(done[i & 1])   # step i - 2 has read this pair; step i - 1 is NOT waited for
+            with torch.cuda.stream(copy_stream):
+                bx, by = bufs[i & 1]
+                bx.copy_(x_host, non_blocking=True)
+                by.copy_(y_host, non_blocking=True)
+                ready[i & 1] = torch.cuda.Event()
+                ready[i & 1].record(copy_stream)
+
         def e2e_step():
-            x_in.copy_(x_host, non_blocking=True)
-            y_in.copy_(y_host, non_blocking=True)
-            loss = step(x_in, y_in)
+            i = pipe['i']
+            pipe['i'] += 1
+            if ready[i & 1] is None:
+                prefetch(i)          # pipeline fill
+            torch.cuda.current_stream().wait_event(ready[i & 1])
+            ready[i & 1] = None
+            prefetch(i + 1)          # crosses PCIe while this step computes
+            loss = run_pair[i & 1]()
+            done[i & 1] = torch.cuda.Event()
+            done[i & 1].record()
             loss_host.copy_(loss.detach().reshape(1), non_blocking=True)
             torch.cuda.current_stream().synchronize()  # the caller reads the loss every step
+
+        for _ in range(2):
+            e2e_step()
+        copy_stream.synchronize()
+        ready[0] = ready[1] = None   # the timed region starts with an empty pipeline
+        pipe['i'] = 0
+        barrier()
 
         ms_e2e = timed_steps(e2e_step)
         t = torch.tensor([ms, ms_e2e], device=dev, dtype=torch.float64)
@@ -341,6 +399,8 @@ def main():
                        'global_batch': 1, 'seq_len': total_t, 'rows_per_gpu': tn,
                        'parallelism': 'sp%d (time axis split, all-gather-KV)' % world,
                        'offset': args.offset,
+                       'e2e_pipeline': 'inputs of step i+1 prefetched on a copy stream while step i computes',
+                       'cuda_graph': graphed is not None,
                        'mask': args.mask + (' (new tensor every %d steps)' % args.mask_refresh
                                             if args.mask_refresh else ' (one tensor for the run)'),
                        'l2': 'L2 flushed between timed steps (256 MB device write outside the per-step event pairs)',
