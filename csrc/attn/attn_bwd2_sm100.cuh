@@ -714,8 +714,8 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd2_cols_kernel(const __g
         // P^T = exp2(scale_log2 S^T - L_i), dS^T = P^T (scale dP^T - scale delta_i): packed pairs along i
         uint32_t pp[16], dd[16];
         const uint32_t sst = stat_off + slot_off;
-#pragma unroll
-        for (int c = 0; c < 8; ++c) {
+        // (one branch per step on "any dead element", not one per group of four: -30 instructions per step)
+        auto chunk = [&](int c, uint32_t m4) {
           const uint4 nl = ld_shared_v4(sst + c * 16);        // -L_i (same address in every lane: broadcast)
           const uint4 nd = ld_shared_v4(sst + 256 + c * 16);  // -scale delta_i
           float x0, x1, x2, x3, t0, t1, t2, t3;
@@ -731,19 +731,24 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_bwd2_cols_kernel(const __g
           x1 = ex2_approx(x1);
           x2 = ex2_approx(x2);
           x3 = ex2_approx(x3);
-          if (mk != 0u) {  // dead elements: P = dS = 0 (also keeps a NaN of a fully masked row's L out)
-            const uint32_t m4 = mk >> (4 * c);
-            if (m4 & 1u) x0 = 0.f, t0 = 0.f;
-            if (m4 & 2u) x1 = 0.f, t1 = 0.f;
-            if (m4 & 4u) x2 = 0.f, t2 = 0.f;
-            if (m4 & 8u) x3 = 0.f, t3 = 0.f;
-          }
+          // dead elements: P = dS = 0 (also keeps a NaN of a fully masked row's L out)
+          if (m4 & 1u) x0 = 0.f, t0 = 0.f;
+          if (m4 & 2u) x1 = 0.f, t1 = 0.f;
+          if (m4 & 4u) x2 = 0.f, t2 = 0.f;
+          if (m4 & 8u) x3 = 0.f, t3 = 0.f;
           fmul2(t0, t1, t0, t1, x0, x1);
           fmul2(t2, t3, t2, t3, x2, x3);
           pp[2 * c] = pack2<T>(x0, x1);
           pp[2 * c + 1] = pack2<T>(x2, x3);
           dd[2 * c] = pack2<T>(t0, t1);
           dd[2 * c + 1] = pack2<T>(t2, t3);
+        };
+        if (mk == 0u) {
+#pragma unroll
+          for (int c = 0; c < 8; ++c) chunk(c, 0u);
+        } else {
+#pragma unroll
+          for (int c = 0; c < 8; ++c) chunk(c, mk >> (4 * c));
         }
         if (!od_ok) mbar_wait(&o_done[s], od_ph ^ 1, 78);  // the stream's previous products have read P^T_s / dS^T_s
         od_ph ^= 1;
