@@ -57,6 +57,19 @@ def bwd_cols():
                                  which=2)
 
 
+def fwd_bwd(reuse):
+    """forward, then both backward kernels reading the forward's gather in place (``reuse``) or gathering again"""
+    def run():
+        fwd()
+        tag = None
+        if reuse and world > 1:
+            hp = runtime.heap()
+            tag = (hp.generation, hp.seq)
+        att.flash_attention_backward(H(k), H(q), H(v), H(g), neg_lse, nds, mask, scale, 1024, H(dk), H(dq), H(dv),
+                                     bits=bits, gather_tag=tag)
+    return run
+
+
 def timed(fn, iters=5):
     for _ in range(2):
         fn()
@@ -81,7 +94,8 @@ def timed(fn, iters=5):
 res = {'world': world, 'heap': runtime.heap().backend if world > 1 else 'none',
        'multicast': bool(runtime.heap().mc_base) if world > 1 else False,
        'fwd_ms': timed(fwd), 'bwd_rows_plus_cols_ms': timed(bwd), 'bwd_rows_ms': timed(bwd_rows),
-       'bwd_cols_ms': timed(bwd_cols)}
+       'bwd_cols_ms': timed(bwd_cols), 'fwd_bwd_regather_ms': timed(fwd_bwd(False)),
+       'fwd_bwd_gather_once_ms': timed(fwd_bwd(True))}
 # the two backward kernels separately (dbg-free: call the C entry points through the same helper with one disabled)
 if rank == 0:
     print(json.dumps(res), flush=True)
