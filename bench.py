@@ -229,6 +229,8 @@ def main():
     # well below the 126 MB L2, so every timed step starts from a cache that a 256 MB write has just evicted.
     flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 
+    step_log = []   # per-step times of this rank, one list per timed region (device-timed, end-to-end)
+
     def timed_steps(fn):
         """K steps, each bracketed by its own CUDA event pair, L2 flushed in between (outside the pairs)."""
         pairs = []
@@ -240,7 +242,9 @@ def main():
             b.record()
             pairs.append((a, b))
         barrier()
-        return sum(a.elapsed_time(b) for a, b in pairs) / args.steps
+        per_step = [a.elapsed_time(b) for a, b in pairs]
+        step_log.append([round(v, 3) for v in per_step])
+        return sum(per_step) / args.steps
 
     result = {'impl': args.impl}
     attention_path = None
@@ -395,6 +399,7 @@ def main():
                       else (('fp32 storage, %s math (mixed precision)' % args.compute_dtype) if args.compute_dtype
                             else 'fp32 storage, tf32 matmul' if args.dtype == 'fp32' else args.dtype)),
             'data': 'synthetic',
+            'step_ms_rank0': {'device': step_log[0], 'e2e': step_log[1]},
             'config': {'model': 'DistributedDotProductAttn heads=%d d_model=%d' % (args.heads, args.d_model),
                        'global_batch': 1, 'seq_len': total_t, 'rows_per_gpu': tn,
                        'parallelism': 'sp%d (time axis split, all-gather-KV)' % world,
