@@ -23,8 +23,10 @@ def test_signatures_match_reference():
     from distributed_dot_product.module import DistributedDotProductAttn
     from distributed_dot_product.multiplication import functions as F
     sig = inspect.signature(DistributedDotProductAttn.__init__)
-    assert list(sig.parameters)[1:] == ['key_dim', 'value_dim', 'query_dim', 'num_heads', 'add_bias', 'offset',
-                                        'distributed']
+    # the reference's seven parameters, in its order; anything this framework adds comes after them with a default
+    assert list(sig.parameters)[1:8] == ['key_dim', 'value_dim', 'query_dim', 'num_heads', 'add_bias', 'offset',
+                                         'distributed']
+    assert all(p.default is not inspect.Parameter.empty for p in list(sig.parameters.values())[8:])
     assert sig.parameters['offset'].default == 32 and sig.parameters['distributed'].default is True
     fwd = inspect.signature(DistributedDotProductAttn.forward)
     assert list(fwd.parameters)[1:] == ['keys', 'queries', 'values', 'attn_mask']
@@ -157,3 +159,24 @@ def test_flash_eligibility_rules():
     assert flash_eligible(*ops(torch.bfloat16, 128, 2, tn=64), mask, 1)
     assert not flash_eligible(*ops(torch.bfloat16, 128, 2, tn=48), mask, 2)    # masked, world > 1: T/N % 32 != 0
     assert not flash_eligible(*ops(torch.bfloat16, 128, 2), mask.float(), 1)   # only bool masks
+
+
+def test_compute_dtype_argument():
+    """``compute_dtype`` (mixed precision on the CUDA path) is validated, keeps the reference's ``state_dict`` and
+    leaves the CPU composition (fp32 parameters, fp32 math) alone."""
+    import pytest
+    from distributed_dot_product.module import DistributedDotProductAttn
+    with pytest.raises(ValueError):
+        DistributedDotProductAttn(32, compute_dtype=torch.float64)
+    torch.manual_seed(0)
+    plain = DistributedDotProductAttn(32, num_heads=2, distributed=False)
+    mixed = DistributedDotProductAttn(32, num_heads=2, distributed=False, compute_dtype=torch.bfloat16)
+    assert list(mixed.state_dict().keys()) == list(plain.state_dict().keys())
+    mixed.load_state_dict(plain.state_dict())
+    x = torch.rand(1, 6, 32)
+    assert torch.equal(mixed(x, x, x), plain(x, x, x))
+
+
+def test_graphed_step_is_importable_without_cuda():
+    from distributed_dot_product.utils.graphs import GraphedStep
+    assert callable(GraphedStep)
