@@ -65,6 +65,8 @@ class ClockSampler(threading.Thread):
         self.stop_flag = threading.Event()
         self.sm, self.reasons, self.max_mhz, self.power = [], set(), None, []
         self.ok = False
+        self.t_begin = self.t_end = None
+        self.wake = threading.Event()
         try:
             import pynvml
             pynvml.nvmlInit()
@@ -86,17 +88,31 @@ class ClockSampler(threading.Thread):
             getattr(nv, 'nvmlClocksThrottleReasonSwPowerCap', 0x4): 'sw_power_cap',
             getattr(nv, 'nvmlClocksThrottleReasonHwPowerBrakeSlowdown', 0x80): 'hw_power_brake',
         }
+        # The thread is started BEFORE the warm-up steps (thread start-up and NVML's first calls stay out of the
+        # timed region); only samples taken between mark_begin() and mark_end() are reported.
         while not self.stop_flag.is_set():
             try:
-                self.sm.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                live = self.t_begin is not None and self.t_end is None
+                sm = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
                 r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
-                for bit, name in names.items():
-                    if r & bit:
-                        self.reasons.add(name)
-                self.power.append(nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0)
+                pw = nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0
+                if live and self.t_end is None:
+                    self.sm.append(sm)
+                    for bit, name in names.items():
+                        if r & bit:
+                            self.reasons.add(name)
+                    self.power.append(pw)
             except Exception:
                 pass
-            time.sleep(0.05)
+            self.wake.wait(0.02 if (self.t_begin is not None and self.t_end is None) else 0.05)
+            self.wake.clear()
+
+    def mark_begin(self):
+        self.t_begin = time.time()
+        self.wake.set()   # sample now, not after the idle-period sleep
+
+    def mark_end(self):
+        self.t_end = time.time()
 
     def summary(self):
         if not self.ok or not self.sm:
@@ -297,12 +313,12 @@ def main():
             elif dtype == torch.float32:
                 attention_path = 'slab (fp32 storage, TF32 tensor-core math)'
         torch.cuda.reset_peak_memory_stats()  # the self-check's slab step must not count as this path's peak
+        sampler = ClockSampler(physical_gpu_index(local_rank))
+        sampler.start()
         for _ in range(max(args.warmup, 3)):
             step(x_dev, y_dev)
         barrier()
         # ---------------- device-timed region
-        sampler = ClockSampler(physical_gpu_index(local_rank))
-        sampler.start()
         # one GPU: the step is replayed from a CUDA graph (one launch instead of ~26); the launch count is taken
         # from an eager step
         graphed = None
@@ -325,7 +341,9 @@ def main():
                 graphed = None
                 torch.cuda.synchronize()
         l0 = count_launches.launch_count if count_launches else 0
+        sampler.mark_begin()
         ms = timed_steps(run_dev)
+        sampler.mark_end()
         launches = (count_launches.launch_count - l0) if count_launches else None
         if graphed is not None:
             launches = per_step_launches * args.steps
