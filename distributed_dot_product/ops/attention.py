@@ -195,6 +195,17 @@ GATHER_REUSE = bool(int(__import__('os').environ.get('DDP_GATHER_REUSE', '1')))
 gather_reuse_count = 0
 
 
+def gather_reusable(gather_tag, generation, seq, which):
+    """May the two backward kernels read the all-gather of the forward call tagged ``gather_tag`` in place?
+
+    Only when (a) reuse is enabled, (b) BOTH kernels run (the row-side call at ``seq + 1`` reads the other parity's
+    workspace; it is the column-side call at ``seq + 2``, which owns that parity and does not push either, that keeps
+    every pushing call into it at ``>= seq + 4``, i.e. behind a wait for the peers' ``seq + 2``), (c) the heap has not
+    been re-allocated and (d) no collective call has used it since the forward."""
+    return bool(GATHER_REUSE and which == 3 and gather_tag is not None and
+                tuple(gather_tag) == (generation, seq))
+
+
 def flash_attention_backward(k4, q4, v4, g4, neg_lse, nds, mask, scale, offset, dk4, dq4, dv4, bits=None,
                              which=3, gather_tag=None):
     """Backward of ``flash_attention_forward`` without any ``[T/N, T]`` slab: two deterministic kernels recompute
@@ -241,7 +252,7 @@ def flash_attention_backward(k4, q4, v4, g4, neg_lse, nds, mask, scale, offset, 
                                     ctypes.byref(nf)))
                 need_ws, need_flags = max(need_ws, ws.value), max(need_flags, nf.value)
         hp.ensure(need_ws, need_flags)
-        if GATHER_REUSE and which == 3 and gather_tag is not None and gather_tag == (hp.generation, hp.seq):
+        if gather_reusable(gather_tag, hp.generation, hp.seq, which):
             reuse_ws = hp.comm[hp.seq & 1].ws[runtime.get_rank()]
             global gather_reuse_count
             gather_reuse_count += 1

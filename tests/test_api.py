@@ -180,3 +180,17 @@ def test_compute_dtype_argument():
 def test_graphed_step_is_importable_without_cuda():
     from distributed_dot_product.utils.graphs import GraphedStep
     assert callable(GraphedStep)
+
+
+def test_gather_reuse_rules(monkeypatch):
+    """When the attention backward may read the forward's all-gather in place (ops/attention.py)."""
+    import distributed_dot_product.ops.attention as att
+    monkeypatch.setattr(att, 'GATHER_REUSE', True)
+    assert att.gather_reusable((3, 7), 3, 7, 3)
+    assert not att.gather_reusable((3, 7), 3, 8, 3)      # another collective call used the heap since the forward
+    assert not att.gather_reusable((3, 7), 4, 7, 3)      # the heap was re-allocated
+    assert not att.gather_reusable((3, 7), 3, 7, 1)      # one kernel only: the parity argument needs both
+    assert not att.gather_reusable((3, 7), 3, 7, 2)
+    assert not att.gather_reusable(None, 3, 7, 3)        # forward ran without a heap (one process) or outside autograd
+    monkeypatch.setattr(att, 'GATHER_REUSE', False)
+    assert not att.gather_reusable((3, 7), 3, 7, 3)
